@@ -1,0 +1,13 @@
+"""autovc_b200 - B200-native (sm_100a) AutoVC generator forward pass behind the reference's Python API.
+
+    from autovc_b200 import AutoEncoder           # drop-in for autovc.auto_encoder.model.AutoEncoder
+    mel, mel_post, codes = AutoEncoder().cuda_forward...   (see model.py)
+
+The compute path is hand-written CUDA in `csrc/` behind the C ABI in `include/autovc_b200.h`; importing this
+package does not need a GPU, running it does (no CPU fallback).
+"""
+from .model import AutoEncoder, overlap_average  # noqa: F401
+from .engine import Engine  # noqa: F401
+from .synth import synth_inputs, synth_state_dict, state_dict_spec  # noqa: F401
+
+__all__ = ["AutoEncoder", "Engine", "overlap_average", "synth_inputs", "synth_state_dict", "state_dict_spec"]

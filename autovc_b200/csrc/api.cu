@@ -1,0 +1,594 @@
+// C ABI of autovc_b200 (see include/autovc_b200.h): context, weight folding/packing, workspace
+// carving and the forward-pass schedule.  Host code only; kernels live in the other .cu files.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/autovc_b200.h"
+#include "common.cuh"
+#include "launch.h"
+
+using namespace avc;
+
+namespace {
+
+thread_local std::string g_create_error = "";
+
+struct Layer {
+    std::string name;
+    int N = 0, K = 0, Kp = 0;        // logical K, padded K (row pitch)
+    int taps = 1, Cin = 0, Cp = 0;   // conv geometry (taps = 1: plain GEMM, Cin = K, Cp = Kp)
+    int w_type = DT_F32;
+    std::vector<float> w, b;         // fp32 masters of the packed matrix [N][Kp] and bias [N]
+    void* w_dev = nullptr;
+    float* b_dev = nullptr;
+};
+
+enum LayerId {
+    L_ENC_CONV0 = 0, L_ENC_CONV1, L_ENC_CONV2,
+    L_ENC_L0_IH, L_ENC_L0_HH, L_ENC_L1_IH, L_ENC_L1_HH,
+    L_DEC_LSTM1_IH, L_DEC_LSTM1_HH,
+    L_DEC_CONV0, L_DEC_CONV1, L_DEC_CONV2,
+    L_DEC_L2_0_IH, L_DEC_L2_0_HH, L_DEC_L2_1_IH, L_DEC_L2_1_HH,
+    L_DEC_LINEAR,
+    L_POST_CONV0, L_POST_CONV1, L_POST_CONV2, L_POST_CONV3, L_POST_CONV4,
+    L_COUNT
+};
+
+const char* kLayerNames[L_COUNT] = {
+    "enc.conv0", "enc.conv1", "enc.conv2",
+    "enc.lstm.l0.ih", "enc.lstm.l0.hh", "enc.lstm.l1.ih", "enc.lstm.l1.hh",
+    "dec.lstm1.ih", "dec.lstm1.hh",
+    "dec.conv0", "dec.conv1", "dec.conv2",
+    "dec.lstm2.l0.ih", "dec.lstm2.l0.hh", "dec.lstm2.l1.ih", "dec.lstm2.l1.hh",
+    "dec.linear",
+    "post.conv0", "post.conv1", "post.conv2", "post.conv3", "post.conv4",
+};
+
+struct Workspace {
+    // all pointers are carved from the caller's workspace; sizes in bytes
+    char* X0; char* actA; char* actB; float* GxE; char* Y0; float* Y1; float* cstate;
+    char* Dm; float* Gd1; char* H1; float* G2; char* H2a; char* H2b; char* melc;
+    size_t total;
+};
+
+}  // namespace
+
+struct avc_ctx {
+    avc_dims dims{};
+    int device = -1;
+    int precision = AVC_PREC_BF16;
+    int num_sms = 148;
+    bool loaded = false;
+    bool force_simt = false;   // AVC_FORCE_SIMT=1: debugging aid, run the GEMMs of the bf16 mode on the CUDA cores
+    std::string err = "";
+    std::map<std::string, std::vector<float>> raw;
+    Layer layers[L_COUNT];
+    int64_t launches = 0;
+    // tensor-core plan cache (valid for one (B,T,workspace) triple)
+    std::vector<TcGemmPlan*> plans;
+    int plan_B = 0, plan_T = 0;
+    void* plan_ws = nullptr;
+    bool plan_encode_only = false;
+    // optional per-phase timing (avc_set_profiling): events at phase boundaries of the last run
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_events;
+    std::vector<int> prof_cats;
+};
+
+namespace {
+
+int fail(avc_ctx* h, int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf; else g_create_error = buf;
+    return code;
+}
+
+int act_type(const avc_ctx* h) { return h->precision == AVC_PREC_FP32 ? DT_F32 : DT_BF16; }
+int post_type(const avc_ctx* h) { return h->precision == AVC_PREC_FP32 ? DT_F32 : DT_F16; }
+
+size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+// ---------------------------------------------------------------------------------------------
+// weight folding / packing (host)
+// ---------------------------------------------------------------------------------------------
+const std::vector<float>* find_raw(avc_ctx* h, const std::string& name, int64_t numel) {
+    auto it = h->raw.find(name);
+    if (it == h->raw.end()) {
+        fail(h, AVC_ERR_MISSING_WEIGHT, "state-dict entry '%s' is missing", name.c_str());
+        return nullptr;
+    }
+    if ((int64_t)it->second.size() != numel) {
+        fail(h, AVC_ERR_MISSING_WEIGHT, "state-dict entry '%s' has %lld elements, expected %lld", name.c_str(),
+             (long long)it->second.size(), (long long)numel);
+        return nullptr;
+    }
+    return &it->second;
+}
+
+// Conv1d(k=5) + eval BatchNorm -> packed [Cout][5*Cp], k = tap*Cp + ci, and folded bias.
+// reference net_layers.py:39-49 (conv), encoder.py:46 (BatchNorm1d, eps 1e-5).
+bool pack_conv(avc_ctx* h, Layer& L, const std::string& prefix, int cin, int cout) {
+    const auto* w = find_raw(h, prefix + ".0.conv.weight", (int64_t)cout * cin * KTAPS);
+    const auto* b = find_raw(h, prefix + ".0.conv.bias", cout);
+    const auto* g = find_raw(h, prefix + ".1.weight", cout);
+    const auto* be = find_raw(h, prefix + ".1.bias", cout);
+    const auto* mu = find_raw(h, prefix + ".1.running_mean", cout);
+    const auto* var = find_raw(h, prefix + ".1.running_var", cout);
+    if (!w || !b || !g || !be || !mu || !var) return false;
+    L.taps = KTAPS; L.Cin = cin; L.Cp = round_up(cin, 64);
+    L.N = cout; L.K = KTAPS * L.Cp; L.Kp = L.K;
+    L.w.assign((size_t)L.N * L.Kp, 0.0f);
+    L.b.assign(L.N, 0.0f);
+    for (int n = 0; n < cout; ++n) {
+        const double s = (double)(*g)[n] / std::sqrt((double)(*var)[n] + 1e-5);
+        L.b[n] = (float)(((double)(*b)[n] - (double)(*mu)[n]) * s + (double)(*be)[n]);
+        for (int ci = 0; ci < cin; ++ci)
+            for (int tap = 0; tap < KTAPS; ++tap)
+                L.w[(size_t)n * L.Kp + tap * L.Cp + ci] = (float)((double)(*w)[((size_t)n * cin + ci) * KTAPS + tap] * s);
+    }
+    return true;
+}
+
+// nn.LSTM matrices -> unit-major gate rows: packed row d*4H + u*4 + g  <-  PyTorch row g*H + u of direction d.
+// ih: [ndir*4H][K] with bias = b_ih + b_hh;  hh: [ndir*4H][H], no bias.
+bool pack_lstm(avc_ctx* h, Layer& Lih, Layer& Lhh, const std::string& prefix, int layer, int in_k, int H, bool bidir) {
+    const int ndir = bidir ? 2 : 1;
+    Lih.taps = 1; Lih.N = ndir * 4 * H; Lih.K = in_k; Lih.Kp = round_up(in_k, 16); Lih.Cin = in_k; Lih.Cp = Lih.Kp;
+    Lhh.taps = 1; Lhh.N = ndir * 4 * H; Lhh.K = H; Lhh.Kp = H; Lhh.Cin = H; Lhh.Cp = H;
+    Lih.w.assign((size_t)Lih.N * Lih.Kp, 0.0f); Lih.b.assign(Lih.N, 0.0f);
+    Lhh.w.assign((size_t)Lhh.N * Lhh.Kp, 0.0f); Lhh.b.assign(Lhh.N, 0.0f);
+    for (int d = 0; d < ndir; ++d) {
+        const std::string sfx = "_l" + std::to_string(layer) + (d ? "_reverse" : "");
+        const auto* wih = find_raw(h, prefix + ".weight_ih" + sfx, (int64_t)4 * H * in_k);
+        const auto* whh = find_raw(h, prefix + ".weight_hh" + sfx, (int64_t)4 * H * H);
+        const auto* bih = find_raw(h, prefix + ".bias_ih" + sfx, 4 * H);
+        const auto* bhh = find_raw(h, prefix + ".bias_hh" + sfx, 4 * H);
+        if (!wih || !whh || !bih || !bhh) return false;
+        for (int u = 0; u < H; ++u)
+            for (int g = 0; g < 4; ++g) {
+                const int src = g * H + u, dst = d * 4 * H + u * 4 + g;
+                memcpy(&Lih.w[(size_t)dst * Lih.Kp], &(*wih)[(size_t)src * in_k], sizeof(float) * in_k);
+                memcpy(&Lhh.w[(size_t)dst * Lhh.Kp], &(*whh)[(size_t)src * H], sizeof(float) * H);
+                Lih.b[dst] = (*bih)[src] + (*bhh)[src];
+            }
+    }
+    return true;
+}
+
+bool pack_linear(avc_ctx* h, Layer& L, const std::string& prefix, int in_k, int out_n) {
+    const auto* w = find_raw(h, prefix + ".weight", (int64_t)out_n * in_k);
+    const auto* b = find_raw(h, prefix + ".bias", out_n);
+    if (!w || !b) return false;
+    L.taps = 1; L.N = out_n; L.K = in_k; L.Kp = round_up(in_k, 16); L.Cin = in_k; L.Cp = L.Kp;
+    L.w.assign((size_t)L.N * L.Kp, 0.0f);
+    for (int n = 0; n < out_n; ++n) memcpy(&L.w[(size_t)n * L.Kp], &(*w)[(size_t)n * in_k], sizeof(float) * in_k);
+    L.b = *b;
+    return true;
+}
+
+int upload_layer(avc_ctx* h, Layer& L) {
+    const size_t n = L.w.size();
+    cudaError_t e;
+    if (L.w_dev) { cudaFree(L.w_dev); L.w_dev = nullptr; }
+    if (L.b_dev) { cudaFree(L.b_dev); L.b_dev = nullptr; }
+    if (L.w_type == DT_F32) {
+        if ((e = cudaMalloc(&L.w_dev, n * 4)) != cudaSuccess) goto bad;
+        if ((e = cudaMemcpy(L.w_dev, L.w.data(), n * 4, cudaMemcpyHostToDevice)) != cudaSuccess) goto bad;
+    } else {
+        std::vector<uint16_t> tmp(n);
+        if (L.w_type == DT_BF16) {
+            for (size_t i = 0; i < n; ++i) { __nv_bfloat16 v = __float2bfloat16_rn(L.w[i]); memcpy(&tmp[i], &v, 2); }
+        } else {
+            for (size_t i = 0; i < n; ++i) {
+                if (std::fabs(L.w[i]) > 65504.0f)
+                    return fail(h, AVC_ERR_UNSUPPORTED, "layer %s: folded weight %g exceeds the fp16 range; use AVC_PREC_FP32",
+                                L.name.c_str(), (double)L.w[i]);
+                __half v = __float2half_rn(L.w[i]); memcpy(&tmp[i], &v, 2);
+            }
+        }
+        if ((e = cudaMalloc(&L.w_dev, n * 2)) != cudaSuccess) goto bad;
+        if ((e = cudaMemcpy(L.w_dev, tmp.data(), n * 2, cudaMemcpyHostToDevice)) != cudaSuccess) goto bad;
+    }
+    if ((e = cudaMalloc((void**)&L.b_dev, L.b.size() * 4)) != cudaSuccess) goto bad;
+    if ((e = cudaMemcpy(L.b_dev, L.b.data(), L.b.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) goto bad;
+    return AVC_OK;
+bad:
+    return fail(h, AVC_ERR_CUDA, "uploading layer %s: %s", L.name.c_str(), cudaGetErrorString(e));
+}
+
+// ---------------------------------------------------------------------------------------------
+// workspace
+// ---------------------------------------------------------------------------------------------
+Workspace carve(const avc_ctx* h, char* base, int B, int T) {
+    const avc_dims& d = h->dims;
+    const size_t as = dtype_size(act_type(h));
+    const size_t M = (size_t)B * T;
+    const int nb = ceil_div(T, d.freq);
+    const int cw = d.dim_pre > CONV_CH ? d.dim_pre : CONV_CH;
+    const int hmax = d.dim_pre > LSTM2_H ? d.dim_pre : LSTM2_H;
+    Workspace w{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align256(bytes); return p; };
+    w.X0 = take(M * (N_MELS + d.dim_emb) * as);
+    w.actA = take(M * cw * as);
+    w.actB = take(M * cw * as);
+    w.GxE = (float*)take(M * 8 * d.dim_neck * 4);
+    w.Y0 = take(M * 2 * d.dim_neck * as);
+    w.Y1 = (float*)take(M * 2 * d.dim_neck * 4);
+    w.cstate = (float*)take((size_t)2 * B * hmax * 4);
+    w.Dm = take((size_t)B * nb * (2 * d.dim_neck + d.dim_emb) * as);
+    w.Gd1 = (float*)take((size_t)B * nb * 4 * d.dim_pre * 4);
+    w.H1 = take(M * d.dim_pre * as);
+    w.G2 = (float*)take(M * 4 * LSTM2_H * 4);
+    w.H2a = take(M * LSTM2_H * as);
+    w.H2b = take(M * LSTM2_H * as);
+    w.melc = take(M * N_MELS * as);
+    w.total = off;
+    return w;
+}
+
+// ---------------------------------------------------------------------------------------------
+// schedule
+// ---------------------------------------------------------------------------------------------
+struct Runner {
+    avc_ctx* h;
+    cudaStream_t s;
+    int B, T;
+    int rc = AVC_OK;
+    size_t plan_cursor = 0;
+    bool building_plans = false;
+
+    bool ok() const { return rc == AVC_OK; }
+    void check(cudaError_t e, const char* what) {
+        if (rc == AVC_OK && e != cudaSuccess) rc = fail(h, AVC_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+    }
+
+    bool use_tc() const { return h->precision == AVC_PREC_BF16 && !h->force_simt; }
+
+    // phase boundary marker for avc_get_profile (no-op unless profiling is on)
+    int cur_cat = -1;
+    void mark(int cat) {
+        if (!h->profiling || cat == cur_cat || !ok()) return;
+        cudaEvent_t ev;
+        if (cudaEventCreate(&ev) != cudaSuccess) return;
+        cudaEventRecord(ev, s);
+        h->prof_events.push_back(ev);
+        h->prof_cats.push_back(cat);
+        cur_cat = cat;
+    }
+
+    // out[m,n] = act(A W^T + b); A is an activation buffer of `a_type`
+    void gemm(int lid, const void* A, int a_type, int lda, int M, int Tutt, int act, void* out, int out_type, int ldo,
+              float* out_t = nullptr, const float* res_t = nullptr) {
+        if (!ok()) return;
+        const Layer& L = h->layers[lid];
+        mark(L.taps > 1 ? AVC_PHASE_CONV : AVC_PHASE_PROJ);
+        GemmParams p{};
+        p.A = A; p.a_type = a_type; p.lda = lda;
+        p.M = M; p.N = L.N; p.K = L.Kp; p.T = Tutt;
+        p.taps = L.taps; p.Cin = L.Cin; p.Cp = L.Cp;
+        p.W = L.w_dev; p.w_type = L.w_type; p.ldw = L.Kp;
+        p.bias = L.b_dev; p.act = act;
+        p.out = out; p.out_type = out_type; p.ldo = ldo;
+        p.out_t = out_t; p.res_t = res_t;
+        if (use_tc()) {
+            if (building_plans) {
+                const char* why = nullptr;
+                TcGemmPlan* plan = tc_gemm_plan_create(p, h->num_sms, &why);
+                if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core GEMM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
+                h->plans.push_back(plan);
+            }
+            check(launch_tc_gemm(h->plans[plan_cursor++], s), L.name.c_str());
+        } else {
+            check(launch_simt_gemm(p, s), L.name.c_str());
+        }
+        h->launches++;
+    }
+
+    // Full-sequence LSTM layer from a hoisted input projection Gx.
+    //   Gx: [B][Tg][ndir*4H] fp32 (row for frame t is t/gx_div);  Y: [B][T][ndir*H] of h_type.
+    void lstm(int lid_hh, const float* Gx, int Tg, int gx_div, void* Y, int h_type, int H, int ndir) {
+        if (!ok()) return;
+        const Layer& L = h->layers[lid_hh];
+        mark(lid_hh <= L_ENC_L1_HH ? AVC_PHASE_ENC_LSTM : (lid_hh == L_DEC_LSTM1_HH ? AVC_PHASE_LSTM1 : AVC_PHASE_LSTM2));
+        const size_t hs = dtype_size(h_type);
+        check(cudaMemsetAsync(wsp->cstate, 0, (size_t)2 * B * H * 4, s), "memset c");
+        const int ldy = ndir * H;
+        for (int step = 0; step < T && ok(); ++step) {
+            LstmStepParams q{};
+            q.h_type = h_type; q.w_type = L.w_type; q.B = B; q.H = H;
+            q.ldh = T * ldy; q.ldho = T * ldy; q.ldg = (long long)Tg * ndir * 4 * H;
+            for (int d = 0; d < ndir; ++d) {
+                const int t = d == 0 ? step : T - 1 - step;
+                const int tp = d == 0 ? t - 1 : t + 1;
+                q.h_prev[d] = step == 0 ? nullptr : (const char*)Y + ((size_t)tp * ldy + d * H) * hs;
+                q.h_out[d] = (char*)Y + ((size_t)t * ldy + d * H) * hs;
+                q.Whh[d] = (const char*)L.w_dev + (size_t)d * 4 * H * H * dtype_size(L.w_type);
+                q.Gx[d] = Gx + (size_t)(t / gx_div) * ndir * 4 * H + (size_t)d * 4 * H;
+                q.c[d] = wsp->cstate + (size_t)d * B * H;
+            }
+            check(launch_simt_lstm_step(q, ndir, s), L.name.c_str());
+            h->launches++;
+        }
+    }
+
+    Workspace* wsp = nullptr;
+};
+
+int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int B, int T, float* mel, float* mel_post,
+        float* codes, void* workspace, size_t workspace_bytes, void* stream, bool encode_only) {
+    if (!h) return AVC_ERR_INVALID_ARG;
+    if (h->device < 0) return fail(h, AVC_ERR_INVALID_ARG, "host-only context (device=-1) cannot run");
+    if (!h->loaded) return fail(h, AVC_ERR_NOT_LOADED, "avc_load_weights has not completed");
+    if (!x || !c_org || !codes || B <= 0 || T <= 0) return fail(h, AVC_ERR_INVALID_ARG, "null pointer or non-positive B/T");
+    if (!encode_only && (!c_trg || !mel || !mel_post)) return fail(h, AVC_ERR_INVALID_ARG, "null c_trg/mel/mel_post");
+    const avc_dims& d = h->dims;
+    if (T < d.freq) return fail(h, AVC_ERR_T_TOO_SHORT, "T=%d < freq=%d: no forward content code exists (the reference raises ValueError)", T, d.freq);
+    Workspace w = carve(h, (char*)workspace, B, T);
+    if (!workspace || workspace_bytes < w.total || ((uintptr_t)workspace & 255))
+        return fail(h, AVC_ERR_WORKSPACE, "workspace must be 256-byte aligned and >= %zu bytes (got %zu)", w.total, workspace_bytes);
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+
+    Runner r{h, (cudaStream_t)stream, B, T};
+    r.wsp = &w;
+    h->launches = 0;
+    for (auto ev : h->prof_events) cudaEventDestroy(ev);
+    h->prof_events.clear(); h->prof_cats.clear();
+    if (r.use_tc()) {
+        const bool hit = h->plan_ws == workspace && h->plan_B == B && h->plan_T == T && h->plan_encode_only == encode_only && !h->plans.empty();
+        if (!hit) {
+            for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+            h->plans.clear();
+            r.building_plans = true;
+            h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_encode_only = encode_only;
+        }
+    }
+
+    const int at = act_type(h), pt = post_type(h);
+    const int M = B * T;
+    const int dn = d.dim_neck, E = d.dim_emb, P = d.dim_pre;
+    const int nb = ceil_div(T, d.freq);
+
+    // ---- encoder (reference encoder.py:53-97) ----
+    r.mark(AVC_PHASE_LAYOUT);
+    r.check(launch_pack_input(x, c_org, w.X0, at, B, T, E, r.s), "pack_input"); h->launches++;
+    r.gemm(L_ENC_CONV0, w.X0, at, N_MELS + E, M, T, ACT_RELU, w.actA, at, CONV_CH);
+    r.gemm(L_ENC_CONV1, w.actA, at, CONV_CH, M, T, ACT_RELU, w.actB, at, CONV_CH);
+    r.gemm(L_ENC_CONV2, w.actB, at, CONV_CH, M, T, ACT_RELU, w.actA, at, CONV_CH);
+    r.gemm(L_ENC_L0_IH, w.actA, at, CONV_CH, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
+    r.lstm(L_ENC_L0_HH, w.GxE, T, 1, w.Y0, at, dn, 2);
+    r.gemm(L_ENC_L1_IH, w.Y0, at, 2 * dn, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
+    r.lstm(L_ENC_L1_HH, w.GxE, T, 1, w.Y1, DT_F32, dn, 2);
+    // code sampling + de-duplicated decoder input (encoder.py:94-95, model.py:99-124)
+    r.mark(AVC_PHASE_LAYOUT);
+    r.check(launch_codes(w.Y1, c_trg, codes, encode_only ? nullptr : w.Dm, at, B, T, dn, E, d.freq, r.s), "codes"); h->launches++;
+
+    if (!encode_only) {
+        // ---- decoder (reference decoder.py:58-79) ----
+        r.gemm(L_DEC_LSTM1_IH, w.Dm, at, 2 * dn + E, B * nb, nb, ACT_NONE, w.Gd1, DT_F32, 4 * P);
+        r.lstm(L_DEC_LSTM1_HH, w.Gd1, nb, d.freq, w.H1, at, P, 1);
+        r.gemm(L_DEC_CONV0, w.H1, at, P, M, T, ACT_RELU, w.actA, at, P);
+        r.gemm(L_DEC_CONV1, w.actA, at, P, M, T, ACT_RELU, w.actB, at, P);
+        r.gemm(L_DEC_CONV2, w.actB, at, P, M, T, ACT_RELU, w.actA, at, P);
+        r.gemm(L_DEC_L2_0_IH, w.actA, at, P, M, T, ACT_NONE, w.G2, DT_F32, 4 * LSTM2_H);
+        r.lstm(L_DEC_L2_0_HH, w.G2, T, 1, w.H2a, at, LSTM2_H, 1);
+        r.gemm(L_DEC_L2_1_IH, w.H2a, at, LSTM2_H, M, T, ACT_NONE, w.G2, DT_F32, 4 * LSTM2_H);
+        r.lstm(L_DEC_L2_1_HH, w.G2, T, 1, w.H2b, at, LSTM2_H, 1);
+        // linear projection -> mel (B,80,T) fp32 + channel-last copy for the postnet (decoder.py:77, model.py:127)
+        r.gemm(L_DEC_LINEAR, w.H2b, at, LSTM2_H, M, T, ACT_NONE, w.melc, pt, N_MELS, mel, nullptr);
+        // ---- postnet + residual (reference postnet.py:50-63, model.py:131-132) ----
+        r.gemm(L_POST_CONV0, w.melc, pt, N_MELS, M, T, ACT_TANH, w.actA, pt, CONV_CH);
+        r.gemm(L_POST_CONV1, w.actA, pt, CONV_CH, M, T, ACT_TANH, w.actB, pt, CONV_CH);
+        r.gemm(L_POST_CONV2, w.actB, pt, CONV_CH, M, T, ACT_TANH, w.actA, pt, CONV_CH);
+        r.gemm(L_POST_CONV3, w.actA, pt, CONV_CH, M, T, ACT_TANH, w.actB, pt, CONV_CH);
+        r.gemm(L_POST_CONV4, w.actB, pt, CONV_CH, M, T, ACT_NONE, nullptr, DT_F32, 0, mel_post, mel);
+    }
+    r.mark(AVC_PHASE_COUNT);  // closing marker
+    if (!r.ok() && r.building_plans) {  // do not keep a half-built plan set
+        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+        h->plans.clear();
+        h->plan_ws = nullptr;
+    }
+    return r.rc;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// extern "C"
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+int avc_abi_version(void) { return 1; }
+
+int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision) {
+    if (!out || !dims) return fail(nullptr, AVC_ERR_INVALID_ARG, "null out/dims");
+    *out = nullptr;
+    if (precision != AVC_PREC_BF16 && precision != AVC_PREC_FP32) return fail(nullptr, AVC_ERR_INVALID_ARG, "precision must be 0 (bf16) or 1 (fp32)");
+    if (dims->dim_neck <= 0 || dims->dim_emb <= 0 || dims->dim_pre <= 0 || dims->freq <= 0)
+        return fail(nullptr, AVC_ERR_INVALID_ARG, "dims must be positive");
+    // kernel constraints: 16-byte vector loads along K and unit-major gate tiles
+    if (dims->dim_neck % 8 || dims->dim_emb % 16 || dims->dim_pre % 64)
+        return fail(nullptr, AVC_ERR_UNSUPPORTED, "need dim_neck %% 8 == 0, dim_emb %% 16 == 0, dim_pre %% 64 == 0 (got %d/%d/%d)",
+                    dims->dim_neck, dims->dim_emb, dims->dim_pre);
+    avc_ctx* h = new (std::nothrow) avc_ctx();
+    if (!h) return fail(nullptr, AVC_ERR_INVALID_ARG, "out of host memory");
+    h->dims = *dims; h->device = device; h->precision = precision;
+    const char* fs = getenv("AVC_FORCE_SIMT");
+    h->force_simt = fs && fs[0] == '1';
+    for (int i = 0; i < L_COUNT; ++i) h->layers[i].name = kLayerNames[i];
+    if (device >= 0) {
+        cudaError_t e = cudaSetDevice(device);
+        cudaDeviceProp prop{};
+        if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
+        if (e != cudaSuccess) { int rc = fail(nullptr, AVC_ERR_CUDA, "cuda device %d: %s", device, cudaGetErrorString(e)); delete h; return rc; }
+        if (prop.major != 10) { int rc = fail(nullptr, AVC_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor); delete h; return rc; }
+        h->num_sms = prop.multiProcessorCount;
+        if (precision == AVC_PREC_BF16 && !h->force_simt) {
+            const char* why = tc_init();
+            if (why) { int rc = fail(nullptr, AVC_ERR_CUDA, "tensor-map driver entry point: %s", why); delete h; return rc; }
+        }
+    }
+    *out = h;
+    return AVC_OK;
+}
+
+int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
+    if (!h || !table || n <= 0) return fail(h, AVC_ERR_INVALID_ARG, "null handle/table");
+    for (int i = 0; i < n; ++i) {
+        if (!table[i].name || !table[i].data || table[i].numel < 0) return fail(h, AVC_ERR_INVALID_ARG, "weight table entry %d is malformed", i);
+        std::string name = table[i].name;
+        if (name.size() > 19 && name.compare(name.size() - 19, 19, "num_batches_tracked") == 0) continue;
+        h->raw[name].assign(table[i].data, table[i].data + table[i].numel);
+    }
+    const avc_dims& d = h->dims;
+    const int dn = d.dim_neck, E = d.dim_emb, P = d.dim_pre;
+    Layer* L = h->layers;
+    bool ok = true;
+    ok = ok && pack_conv(h, L[L_ENC_CONV0], "encoder.convolutions.0", N_MELS + E, CONV_CH);
+    ok = ok && pack_conv(h, L[L_ENC_CONV1], "encoder.convolutions.1", CONV_CH, CONV_CH);
+    ok = ok && pack_conv(h, L[L_ENC_CONV2], "encoder.convolutions.2", CONV_CH, CONV_CH);
+    ok = ok && pack_lstm(h, L[L_ENC_L0_IH], L[L_ENC_L0_HH], "encoder.lstm", 0, CONV_CH, dn, true);
+    ok = ok && pack_lstm(h, L[L_ENC_L1_IH], L[L_ENC_L1_HH], "encoder.lstm", 1, 2 * dn, dn, true);
+    ok = ok && pack_lstm(h, L[L_DEC_LSTM1_IH], L[L_DEC_LSTM1_HH], "decoder.lstm1", 0, 2 * dn + E, P, false);
+    ok = ok && pack_conv(h, L[L_DEC_CONV0], "decoder.convolutions.0", P, P);
+    ok = ok && pack_conv(h, L[L_DEC_CONV1], "decoder.convolutions.1", P, P);
+    ok = ok && pack_conv(h, L[L_DEC_CONV2], "decoder.convolutions.2", P, P);
+    ok = ok && pack_lstm(h, L[L_DEC_L2_0_IH], L[L_DEC_L2_0_HH], "decoder.lstm2", 0, P, LSTM2_H, false);
+    ok = ok && pack_lstm(h, L[L_DEC_L2_1_IH], L[L_DEC_L2_1_HH], "decoder.lstm2", 1, LSTM2_H, LSTM2_H, false);
+    ok = ok && pack_linear(h, L[L_DEC_LINEAR], "decoder.linear_projection.linear_layer", LSTM2_H, N_MELS);
+    ok = ok && pack_conv(h, L[L_POST_CONV0], "postnet.convolutions.0", N_MELS, CONV_CH);
+    ok = ok && pack_conv(h, L[L_POST_CONV1], "postnet.convolutions.1", CONV_CH, CONV_CH);
+    ok = ok && pack_conv(h, L[L_POST_CONV2], "postnet.convolutions.2", CONV_CH, CONV_CH);
+    ok = ok && pack_conv(h, L[L_POST_CONV3], "postnet.convolutions.3", CONV_CH, CONV_CH);
+    ok = ok && pack_conv(h, L[L_POST_CONV4], "postnet.convolutions.4", CONV_CH, N_MELS);
+    if (!ok) { h->loaded = false; return AVC_ERR_MISSING_WEIGHT; }
+    h->raw.clear();
+    for (int i = 0; i < L_COUNT; ++i) {
+        const bool post = i >= L_POST_CONV0;
+        L[i].w_type = h->precision == AVC_PREC_FP32 ? DT_F32 : (post ? DT_F16 : DT_BF16);
+    }
+    if (h->device >= 0) {
+        cudaError_t e = cudaSetDevice(h->device);
+        if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+        for (int i = 0; i < L_COUNT; ++i) {
+            int rc = upload_layer(h, L[i]);
+            if (rc != AVC_OK) return rc;
+        }
+        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+        h->plans.clear();
+        h->plan_ws = nullptr;
+    }
+    h->loaded = true;
+    return AVC_OK;
+}
+
+size_t avc_workspace_bytes(avc_handle h, int B, int T) {
+    if (!h || B <= 0 || T <= 0) return 0;
+    return carve(h, nullptr, B, T).total;
+}
+
+int avc_forward(avc_handle h, const float* x, const float* c_org, const float* c_trg, int B, int T, float* mel,
+                float* mel_post, float* codes, void* workspace, size_t workspace_bytes, void* stream) {
+    return run(h, x, c_org, c_trg, B, T, mel, mel_post, codes, workspace, workspace_bytes, stream, false);
+}
+
+int avc_encode(avc_handle h, const float* x, const float* c_org, int B, int T, float* codes, void* workspace,
+               size_t workspace_bytes, void* stream) {
+    return run(h, x, c_org, nullptr, B, T, nullptr, nullptr, codes, workspace, workspace_bytes, stream, true);
+}
+
+int64_t avc_last_launch_count(avc_handle h) { return h ? h->launches : 0; }
+
+int avc_set_profiling(avc_handle h, int enable) {
+    if (!h) return AVC_ERR_INVALID_ARG;
+    h->profiling = enable != 0;
+    return AVC_OK;
+}
+
+int avc_get_profile(avc_handle h, float* ms, int n) {
+    if (!h || !ms || n < AVC_PHASE_COUNT) return fail(h, AVC_ERR_INVALID_ARG, "need room for %d phases", (int)AVC_PHASE_COUNT);
+    for (int i = 0; i < n; ++i) ms[i] = 0.0f;
+    if (h->prof_events.size() < 2) return fail(h, AVC_ERR_INVALID_ARG, "no profiled run recorded");
+    cudaError_t e = cudaEventSynchronize(h->prof_events.back());
+    if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaEventSynchronize: %s", cudaGetErrorString(e));
+    for (size_t i = 0; i + 1 < h->prof_events.size(); ++i) {
+        float t = 0.0f;
+        cudaEventElapsedTime(&t, h->prof_events[i], h->prof_events[i + 1]);
+        ms[h->prof_cats[i]] += t;
+    }
+    return AVC_PHASE_COUNT;
+}
+
+int64_t avc_debug_packed(avc_handle h, const char* which, float* out, int64_t cap) {
+    if (!h || !which) return AVC_ERR_INVALID_ARG;
+    if (!h->loaded) return fail(h, AVC_ERR_NOT_LOADED, "weights not loaded");
+    std::string s = which;
+    if (s.size() < 3) return fail(h, AVC_ERR_INVALID_ARG, "bad blob name '%s'", which);
+    const std::string lname = s.substr(0, s.size() - 2), kind = s.substr(s.size() - 2);
+    for (int i = 0; i < L_COUNT; ++i) {
+        if (h->layers[i].name != lname) continue;
+        const std::vector<float>& v = kind == ".w" ? h->layers[i].w : h->layers[i].b;
+        if (kind != ".w" && kind != ".b") break;
+        if (out) memcpy(out, v.data(), sizeof(float) * (size_t)std::min<int64_t>(cap, (int64_t)v.size()));
+        return (int64_t)v.size();
+    }
+    return fail(h, AVC_ERR_INVALID_ARG, "unknown packed blob '%s'", which);
+}
+
+int avc_debug_gemm(avc_handle h, const char* layer, int use_tc, const void* A, int a_type, int lda, int M, int T, int act,
+                   void* out, int out_type, int ldo, float* out_t, const float* res_t, void* stream) {
+    if (!h || !layer || !A) return fail(h, AVC_ERR_INVALID_ARG, "null argument");
+    if (!h->loaded || h->device < 0) return fail(h, AVC_ERR_NOT_LOADED, "weights not loaded on a device");
+    for (int i = 0; i < L_COUNT; ++i) {
+        const Layer& L = h->layers[i];
+        if (L.name != layer) continue;
+        GemmParams p{};
+        p.A = A; p.a_type = a_type; p.lda = lda; p.M = M; p.N = L.N; p.K = L.Kp; p.T = T;
+        p.taps = L.taps; p.Cin = L.Cin; p.Cp = L.Cp; p.W = L.w_dev; p.w_type = L.w_type; p.ldw = L.Kp;
+        p.bias = L.b_dev; p.act = act; p.out = out; p.out_type = out_type; p.ldo = ldo; p.out_t = out_t; p.res_t = res_t;
+        cudaError_t e;
+        if (use_tc) {
+            const char* why = tc_init();
+            if (why) return fail(h, AVC_ERR_CUDA, "%s", why);
+            TcGemmPlan* plan = tc_gemm_plan_create(p, h->num_sms, &why);
+            if (!plan) return fail(h, AVC_ERR_UNSUPPORTED, "tensor-core GEMM plan for %s: %s", layer, why ? why : "?");
+            e = launch_tc_gemm(plan, (cudaStream_t)stream);
+            tc_gemm_plan_destroy(plan);   // tensor maps are passed by value at launch
+        } else {
+            e = launch_simt_gemm(p, (cudaStream_t)stream);
+        }
+        if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "%s: %s", layer, cudaGetErrorString(e));
+        return AVC_OK;
+    }
+    return fail(h, AVC_ERR_INVALID_ARG, "unknown layer '%s'", layer);
+}
+
+void avc_destroy(avc_handle h) {
+    if (!h) return;
+    if (h->device >= 0) {
+        cudaSetDevice(h->device);
+        for (int i = 0; i < L_COUNT; ++i) {
+            if (h->layers[i].w_dev) cudaFree(h->layers[i].w_dev);
+            if (h->layers[i].b_dev) cudaFree(h->layers[i].b_dev);
+        }
+        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+        for (auto ev : h->prof_events) cudaEventDestroy(ev);
+    }
+    delete h;
+}
+
+const char* avc_last_error(avc_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+}  // extern "C"

@@ -1,0 +1,24 @@
+// Host-side launcher declarations shared between the translation units.
+#pragma once
+#include "common.cuh"
+
+namespace avc {
+
+// simt_kernels.cu
+cudaError_t launch_simt_gemm(const GemmParams& p, cudaStream_t s);
+cudaError_t launch_simt_lstm_step(const LstmStepParams& q, int ndir, cudaStream_t s);
+cudaError_t launch_pack_input(const float* x, const float* c_org, void* X0, int out_type, int B, int T, int E,
+                              cudaStream_t s);
+cudaError_t launch_codes(const float* Y, const float* c_trg, float* codes, void* D, int d_type, int B, int T, int dn,
+                         int E, int freq, cudaStream_t s);
+
+// tc_gemm.cu (tcgen05 + TMA implicit-GEMM)
+struct TcGemmPlan;  // opaque: tensor maps + tiling for one (layer, B, T) instance
+// Returns nullptr and sets *err when the shape is not supported by the tensor-core kernel.
+TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** err);
+void tc_gemm_plan_destroy(TcGemmPlan* plan);
+cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s);
+// one-time driver entry point lookup; returns nullptr on success or an error string
+const char* tc_init();
+
+}  // namespace avc

@@ -1,0 +1,324 @@
+// CUDA-core (SIMT) kernels: the fp32 validation path of every layer, plus the small layout kernels
+// (input packing, code sampling) shared by both precisions.
+//
+// The validation mode exists to hold the reference to <= 1e-4 (north-star) - fp32 operands, fp32 FFMA
+// accumulation, accurate expf/tanhf - and as the on-device cross-check for the tcgen05 path.
+#include "common.cuh"
+#include "launch.h"
+
+namespace avc {
+
+// ---------------------------------------------------------------------------------------------
+// element helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 load4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 load4(const __nv_bfloat16* p) {
+    uint2 r = *reinterpret_cast<const uint2*>(p);
+    __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&r.x), b = *reinterpret_cast<__nv_bfloat162*>(&r.y);
+    float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+    return make_float4(fa.x, fa.y, fb.x, fb.y);
+}
+__device__ __forceinline__ float4 load4(const __half* p) {
+    uint2 r = *reinterpret_cast<const uint2*>(p);
+    __half2 a = *reinterpret_cast<__half2*>(&r.x), b = *reinterpret_cast<__half2*>(&r.y);
+    float2 fa = __half22float2(a), fb = __half22float2(b);
+    return make_float4(fa.x, fa.y, fb.x, fb.y);
+}
+__device__ __forceinline__ void store4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void store4(__nv_bfloat16* p, float4 v) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 r;
+    r.x = *reinterpret_cast<uint32_t*>(&a);
+    r.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(p) = r;
+}
+__device__ __forceinline__ void store4(__half* p, float4 v) {
+    __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+    uint2 r;
+    r.x = *reinterpret_cast<uint32_t*>(&a);
+    r.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(p) = r;
+}
+__device__ __forceinline__ void store1(float* p, float v) { *p = v; }
+__device__ __forceinline__ void store1(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+__device__ __forceinline__ void store1(__half* p, float v) { *p = __float2half_rn(v); }
+
+__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == ACT_RELU) return fmaxf(v, 0.0f);
+    if (act == ACT_TANH) return tanhf(v);
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 64x64x16 register-tiled FFMA main loop (256 threads, 4x4 per thread, double-buffered smem)
+// ---------------------------------------------------------------------------------------------
+constexpr int BM = 64, BN = 64, BK = 16, PITCH = 68;
+
+template <typename TW, typename ALoad>
+__device__ __forceinline__ void simt_mainloop(float (&acc)[4][4], ALoad a_load, const TW* __restrict__ W, int ldw,
+                                              int n0, int N, int K) {
+    __shared__ __align__(16) float As[2][BK][PITCH];
+    __shared__ __align__(16) float Ws[2][BK][PITCH];
+    const int tid = threadIdx.x;
+    const int lr = tid >> 2;         // tile row (A) / tile column (W) this thread stages
+    const int kq = (tid & 3) * 4;    // k offset inside the BK slab
+    const int tx = tid & 15, ty = tid >> 4;
+    const bool w_ok = (n0 + lr) < N;
+    const TW* wrow = W + (size_t)(n0 + lr) * ldw;
+
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+
+    float4 ra = a_load(kq);
+    float4 rw = w_ok ? load4(wrow + kq) : make_float4(0.f, 0.f, 0.f, 0.f);
+    int buf = 0;
+    As[0][kq + 0][lr] = ra.x; As[0][kq + 1][lr] = ra.y; As[0][kq + 2][lr] = ra.z; As[0][kq + 3][lr] = ra.w;
+    Ws[0][kq + 0][lr] = rw.x; Ws[0][kq + 1][lr] = rw.y; Ws[0][kq + 2][lr] = rw.z; Ws[0][kq + 3][lr] = rw.w;
+    __syncthreads();
+
+    for (int k0 = 0; k0 < K; k0 += BK) {
+        const bool more = (k0 + BK) < K;
+        if (more) {
+            ra = a_load(k0 + BK + kq);
+            rw = w_ok ? load4(wrow + k0 + BK + kq) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
+            const float4 w = *reinterpret_cast<const float4*>(&Ws[buf][k][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+            const float wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
+        }
+        if (more) {
+            const int nb = buf ^ 1;
+            As[nb][kq + 0][lr] = ra.x; As[nb][kq + 1][lr] = ra.y; As[nb][kq + 2][lr] = ra.z; As[nb][kq + 3][lr] = ra.w;
+            Ws[nb][kq + 0][lr] = rw.x; Ws[nb][kq + 1][lr] = rw.y; Ws[nb][kq + 2][lr] = rw.z; Ws[nb][kq + 3][lr] = rw.w;
+            __syncthreads();
+            buf = nb;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// GEMM / implicit conv1d with fused bias + activation (+ channel-first fp32 output + residual)
+// ---------------------------------------------------------------------------------------------
+template <typename TA, typename TW, typename TO>
+__global__ void __launch_bounds__(256) simt_gemm_kernel(GemmParams p) {
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const int tid = threadIdx.x;
+    const int lr = tid >> 2;
+    const int m = m0 + lr;
+    const int t_row = (p.taps > 1) ? (m % p.T) : 0;
+    const int pad = p.taps / 2;
+    const TA* A = reinterpret_cast<const TA*>(p.A);
+    const bool m_ok = m < p.M;
+
+    auto a_load = [&](int k) -> float4 {
+        if (!m_ok) return make_float4(0.f, 0.f, 0.f, 0.f);
+        int tap = 0, ci = k;
+        if (p.taps > 1) { tap = k / p.Cp; ci = k - tap * p.Cp; }
+        if (ci >= p.Cin) return make_float4(0.f, 0.f, 0.f, 0.f);
+        const int tt = t_row + tap - pad;
+        if (p.taps > 1 && (tt < 0 || tt >= p.T)) return make_float4(0.f, 0.f, 0.f, 0.f);
+        return load4(A + (size_t)(m + tap - pad) * p.lda + ci);
+    };
+
+    float acc[4][4];
+    simt_mainloop<TW>(acc, a_load, reinterpret_cast<const TW*>(p.W), p.ldw, n0, p.N, p.K);
+
+    const int tx = tid & 15, ty = tid >> 4;
+    const int n = n0 + tx * 4;
+    if (n >= p.N) return;
+    const float4 bv = p.bias ? *reinterpret_cast<const float4*>(p.bias + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int mm = m0 + ty * 4 + i;
+        if (mm >= p.M) continue;
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = apply_act(acc[i][j] + bb[j], p.act);
+        if (p.out) store4(reinterpret_cast<TO*>(p.out) + (size_t)mm * p.ldo + n, make_float4(v[0], v[1], v[2], v[3]));
+        if (p.out_t) {
+            const int b = mm / p.T, t = mm - b * p.T;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const size_t o = ((size_t)b * p.N + (n + j)) * p.T + t;
+                p.out_t[o] = v[j] + (p.res_t ? p.res_t[o] : 0.0f);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// One LSTM time step (recurrent GEMM + fused gate math), both directions via blockIdx.z
+// ---------------------------------------------------------------------------------------------
+template <typename TH, typename TW>
+__global__ void __launch_bounds__(256) simt_lstm_step_kernel(LstmStepParams q) {
+    const int d = blockIdx.z;
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const int tid = threadIdx.x;
+    const int lr = tid >> 2;
+    const int b_ld = m0 + lr;
+    const TH* hp = reinterpret_cast<const TH*>(q.h_prev[d]);
+    const bool ok = (b_ld < q.B) && (hp != nullptr);
+
+    auto a_load = [&](int k) -> float4 {
+        if (!ok) return make_float4(0.f, 0.f, 0.f, 0.f);
+        return load4(hp + (size_t)b_ld * q.ldh + k);
+    };
+    float acc[4][4];
+    if (hp != nullptr) {
+        simt_mainloop<TW>(acc, a_load, reinterpret_cast<const TW*>(q.Whh[d]), q.H, n0, 4 * q.H, q.H);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+    }
+
+    const int tx = tid & 15, ty = tid >> 4;
+    const int n = n0 + tx * 4;
+    const int u = n >> 2;
+    if (u >= q.H) return;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int b = m0 + ty * 4 + i;
+        if (b >= q.B) continue;
+        const float4 gx = *reinterpret_cast<const float4*>(q.Gx[d] + (size_t)b * q.ldg + n);
+        const float ig = sigmoid_acc(acc[i][0] + gx.x);
+        const float fg = sigmoid_acc(acc[i][1] + gx.y);
+        const float gg = tanhf(acc[i][2] + gx.z);
+        const float og = sigmoid_acc(acc[i][3] + gx.w);
+        float* cp = q.c[d] + (size_t)b * q.H + u;
+        const float c_new = fg * (*cp) + ig * gg;
+        *cp = c_new;
+        store1(reinterpret_cast<TH*>(q.h_out[d]) + (size_t)b * q.ldho + u, og * tanhf(c_new));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Layout kernels
+// ---------------------------------------------------------------------------------------------
+// x (B,80,T) fp32 channel-first + c_org (B,E) -> X0 (B,T,80+E) channel-last of type TO.
+// reference encoder.py:65-66 (expand + cat) without materialising the fp32 concat.
+template <typename TO>
+__global__ void pack_input_kernel(const float* __restrict__ x, const float* __restrict__ c_org, TO* __restrict__ X0,
+                                  int B, int T, int E) {
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z;
+    const int t0 = blockIdx.x * 32;
+    const int C = N_MELS + E;
+    const int tx = threadIdx.x, ty = threadIdx.y;  // 32 x 8
+    // mel part: transpose 32(t) x 32(c) tiles
+    for (int c0 = 0; c0 < N_MELS; c0 += 32) {
+        for (int j = ty; j < 32; j += 8) {
+            const int c = c0 + j, t = t0 + tx;
+            tile[j][tx] = (c < N_MELS && t < T) ? x[((size_t)b * N_MELS + c) * T + t] : 0.0f;
+        }
+        __syncthreads();
+        for (int j = ty; j < 32; j += 8) {
+            const int t = t0 + j, c = c0 + tx;
+            if (t < T && c < N_MELS) store1(X0 + ((size_t)b * T + t) * C + c, tile[tx][j]);
+        }
+        __syncthreads();
+    }
+    // speaker part: broadcast over t
+    for (int j = ty; j < 32; j += 8) {
+        const int t = t0 + j;
+        if (t >= T) continue;
+        for (int e = tx; e < E; e += 32) store1(X0 + ((size_t)b * T + t) * C + N_MELS + e, c_org[(size_t)b * E + e]);
+    }
+}
+
+// Encoder output Y (B,T,2*dn) fp32 -> content codes (reference encoder.py:94-95, model.py:99,143) and,
+// when D != nullptr, the de-duplicated decoder input D (B, nb, 2*dn+E): one row per distinct column of the
+// reference's up-sampled (B,320,T) tensor (model.py:115-124) - fwd code min(s,nf-1) | bwd code s | c_trg.
+template <typename TO>
+__global__ void codes_kernel(const float* __restrict__ Y, const float* __restrict__ c_trg, float* __restrict__ codes,
+                             TO* __restrict__ D, int B, int T, int dn, int E, int freq) {
+    const int b = blockIdx.x;
+    const int nf = T / freq, nb = (T + freq - 1) / freq;
+    const int ldy = 2 * dn;
+    for (int i = threadIdx.x; i < nf * dn; i += blockDim.x) {
+        const int j = i / dn, u = i - j * dn;
+        codes[(size_t)b * dn * (nf + nb) + i] = Y[((size_t)b * T + (j * freq + freq - 1)) * ldy + u];
+    }
+    for (int i = threadIdx.x; i < nb * dn; i += blockDim.x) {
+        const int j = i / dn, u = i - j * dn;
+        codes[(size_t)b * dn * (nf + nb) + nf * dn + i] = Y[((size_t)b * T + j * freq) * ldy + dn + u];
+    }
+    if (D == nullptr) return;
+    const int CD = 2 * dn + E;
+    for (int i = threadIdx.x; i < nb * CD; i += blockDim.x) {
+        const int s = i / CD, c = i - s * CD;
+        float v;
+        if (c < dn) {
+            const int j = min(s, nf - 1);
+            v = Y[((size_t)b * T + (j * freq + freq - 1)) * ldy + c];
+        } else if (c < 2 * dn) {
+            v = Y[((size_t)b * T + s * freq) * ldy + c];
+        } else {
+            v = c_trg[(size_t)b * E + (c - 2 * dn)];
+        }
+        store1(D + ((size_t)b * nb + s) * CD + c, v);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------------------------
+template <typename TA, typename TW>
+static cudaError_t launch_simt_gemm_o(const GemmParams& p, cudaStream_t s) {
+    dim3 grid(ceil_div(p.M, BM), ceil_div(p.N, BN));
+    switch (p.out_type) {
+        case DT_F32: simt_gemm_kernel<TA, TW, float><<<grid, 256, 0, s>>>(p); break;
+        case DT_BF16: simt_gemm_kernel<TA, TW, __nv_bfloat16><<<grid, 256, 0, s>>>(p); break;
+        default: simt_gemm_kernel<TA, TW, __half><<<grid, 256, 0, s>>>(p); break;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_simt_gemm(const GemmParams& p, cudaStream_t s) {
+    if (p.a_type == DT_F32 && p.w_type == DT_F32) return launch_simt_gemm_o<float, float>(p, s);
+    if (p.a_type == DT_BF16 && p.w_type == DT_BF16) return launch_simt_gemm_o<__nv_bfloat16, __nv_bfloat16>(p, s);
+    if (p.a_type == DT_F16 && p.w_type == DT_F16) return launch_simt_gemm_o<__half, __half>(p, s);
+    if (p.a_type == DT_F32 && p.w_type == DT_BF16) return launch_simt_gemm_o<float, __nv_bfloat16>(p, s);
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_simt_lstm_step(const LstmStepParams& q, int ndir, cudaStream_t s) {
+    dim3 grid(ceil_div(q.B, BM), ceil_div(4 * q.H, BN), ndir);
+    if (q.h_type == DT_F32 && q.w_type == DT_F32) simt_lstm_step_kernel<float, float><<<grid, 256, 0, s>>>(q);
+    else if (q.h_type == DT_BF16 && q.w_type == DT_BF16) simt_lstm_step_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, s>>>(q);
+    else if (q.h_type == DT_F32 && q.w_type == DT_BF16) simt_lstm_step_kernel<float, __nv_bfloat16><<<grid, 256, 0, s>>>(q);
+    else return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_input(const float* x, const float* c_org, void* X0, int out_type, int B, int T, int E,
+                              cudaStream_t s) {
+    dim3 grid(ceil_div(T, 32), 1, B), block(32, 8);
+    if (out_type == DT_F32) pack_input_kernel<float><<<grid, block, 0, s>>>(x, c_org, (float*)X0, B, T, E);
+    else if (out_type == DT_BF16) pack_input_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(x, c_org, (__nv_bfloat16*)X0, B, T, E);
+    else pack_input_kernel<__half><<<grid, block, 0, s>>>(x, c_org, (__half*)X0, B, T, E);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_codes(const float* Y, const float* c_trg, float* codes, void* D, int d_type, int B, int T, int dn,
+                         int E, int freq, cudaStream_t s) {
+    if (d_type == DT_F32) codes_kernel<float><<<B, 256, 0, s>>>(Y, c_trg, codes, (float*)D, B, T, dn, E, freq);
+    else if (d_type == DT_BF16) codes_kernel<__nv_bfloat16><<<B, 256, 0, s>>>(Y, c_trg, codes, (__nv_bfloat16*)D, B, T, dn, E, freq);
+    else codes_kernel<__half><<<B, 256, 0, s>>>(Y, c_trg, codes, (__half*)D, B, T, dn, E, freq);
+    return cudaGetLastError();
+}
+
+}  // namespace avc

@@ -1,0 +1,329 @@
+// Tensor-core implicit-GEMM for the conv1d(k=5) / projection / linear layers (sm_100a):
+//   TMA (cp.async.bulk.tensor, 128-byte swizzle) -> shared memory ring -> tcgen05.mma (bf16|fp16 x bf16|fp16 -> fp32
+//   accumulators in TMEM, double-buffered) -> tcgen05.ld epilogue with fused bias(+folded BatchNorm) + ReLU/tanh,
+//   writing bf16/fp16/fp32 channel-last activations and/or the reference's fp32 channel-first (B,80,T) layout
+//   (+ the postnet residual).
+//
+// The convolution's zero padding (reference net_layers.py:39, padding=2) is the TMA out-of-bounds zero fill:
+// activations are a 3-D tensor (C, T, B) and the tile for tap k is fetched at time coordinate t0 + k - 2, so rows
+// that fall outside [0,T) of the SAME utterance arrive as zeros and no padded copy is ever materialised.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
+// warps 2..5 = epilogue (TMEM lane quarter = warp_id % 4).  Persistent over output tiles.
+#include <cstdio>
+#include <cuda.h>
+
+#include "common.cuh"
+#include "launch.h"
+#include "ptx.cuh"
+
+namespace avc {
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;                       // 64 x 2 B = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
+constexpr int SMEM_BUDGET = 200 * 1024;
+
+struct TcGemmArgs {
+    int N;
+    int taps, kblocks_per_tap, Cp, pad;
+    int gT, gB, TB, BB;                  // tiling geometry: rows = (b, t), tile = BB utterances x TB frames
+    int tiles_t, tiles_n, num_tiles;
+    int T;                               // true frames per utterance (channel-first output addressing)
+    const float* bias;
+    int act;
+    void* out; int out_type; int ldo;
+    float* out_t; const float* res_t;
+    uint32_t idesc;
+};
+
+template <int BLOCK_N>
+struct Cfg {
+    static constexpr int W_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_STAGE_BYTES + W_STAGE_BYTES;
+    static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
+    static constexpr int ACC_STRIDE = BLOCK_N <= 128 ? 128 : 256;   // TMEM columns per accumulator stage
+    static constexpr uint32_t TMEM_COLS = 2 * ACC_STRIDE;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static_assert(W_STAGE_BYTES % 1024 == 0, "stage buffers must stay 1024-byte aligned for SWIZZLE_128B");
+};
+
+__device__ __forceinline__ float fast_tanh(float x) {
+    // tanh(x) = 1 - 2/(1+e^{2x}); ex2.approx + fast division: abs error ~1e-6 (tanh.approx.f32 is ~5e-4, too coarse
+    // for the 1e-2 end-to-end budget through four postnet layers)
+    const float e = __expf(2.0f * x);
+    return 1.0f - __fdividef(2.0f, 1.0f + e);
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(192, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const TcGemmArgs a) {
+    using C = Cfg<BLOCK_N>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sW = smem + C::STAGES * A_STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + C::STAGES;
+    uint64_t* tfull = bars + 2 * C::STAGES;
+    uint64_t* tempty = tfull + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_kb = a.taps * a.kblocks_per_tap;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmW);
+        for (int i = 0; i < C::STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tfull[i], 1); ptx::mbar_init(&tempty[i], 128); }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<C::TMEM_COLS>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+                const int nt = tile % a.tiles_n, mt = tile / a.tiles_n;
+                const int t0 = (mt % a.tiles_t) * a.TB, b0 = (mt / a.tiles_t) * a.BB;
+                const int n0 = nt * BLOCK_N;
+                for (int tap = 0; tap < a.taps; ++tap) {
+                    for (int kc = 0; kc < a.kblocks_per_tap; ++kc) {
+                        ptx::mbar_wait(&empty[stage], phase ^ 1);
+                        ptx::mbar_expect_tx(&full[stage], C::STAGE_BYTES);
+                        ptx::tma_load_3d(sA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BLOCK_K, t0 + tap - a.pad, b0);
+                        ptx::tma_load_2d(sW + stage * C::W_STAGE_BYTES, &tmW, &full[stage], tap * a.Cp + kc * BLOCK_K, n0);
+                        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            int as = 0; uint32_t aphase = 0;
+            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+                ptx::mbar_wait(&tempty[as], aphase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(as * C::ACC_STRIDE);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    ptx::mbar_wait(&full[stage], phase);
+                    ptx::tc_fence_after();
+                    const uint64_t adesc = ptx::umma_desc_sw128(ptx::smem_u32(sA + stage * A_STAGE_BYTES));
+                    const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sW + stage * C::W_STAGE_BYTES));
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        // advance 32 bytes (16 elements) along K inside the swizzle row: +2 in the (addr>>4) field
+                        ptx::umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    ptx::umma_commit(&empty[stage]);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+                ptx::umma_commit(&tfull[as]);
+                if (++as == 2) { as = 0; aphase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int q = warp & 3;                 // TMEM lane quarter this warp may access
+        const int r = q * 32 + lane;            // tile row
+        int as = 0; uint32_t aphase = 0;
+        for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+            const int nt = tile % a.tiles_n, mt = tile / a.tiles_n;
+            const int t = (mt % a.tiles_t) * a.TB + (r % a.TB);
+            const int b = (mt / a.tiles_t) * a.BB + (r / a.TB);
+            const bool valid = (t < a.gT) && (b < a.gB);
+            const size_t m = (size_t)b * a.gT + t;
+            const int n0 = nt * BLOCK_N;
+            // channel-first addressing uses the true utterance length
+            size_t ot_base = 0;
+            if (a.out_t) { const size_t bb = m / a.T, tt = m - bb * a.T; ot_base = (bb * a.N) * a.T + tt; }
+
+            ptx::mbar_wait(&tfull[as], aphase);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE);
+#pragma unroll 1
+            for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
+                uint32_t rr[16];
+                ptx::tmem_ld16(taddr + (uint32_t)c0, rr);
+                ptx::tmem_ld_wait();
+                float v[16];
+                const int n = n0 + c0;
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) {
+                    const float4 bv = a.bias ? __ldg(reinterpret_cast<const float4*>(a.bias + n + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v[j + 0] = __uint_as_float(rr[j + 0]) + bv.x;
+                    v[j + 1] = __uint_as_float(rr[j + 1]) + bv.y;
+                    v[j + 2] = __uint_as_float(rr[j + 2]) + bv.z;
+                    v[j + 3] = __uint_as_float(rr[j + 3]) + bv.w;
+                }
+                if (a.act == ACT_RELU) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.0f);
+                } else if (a.act == ACT_TANH) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = fast_tanh(v[j]);
+                }
+                if (valid) {
+                    if (a.out) {
+                        if (a.out_type == DT_F32) {
+                            float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(a.out) + m * a.ldo + n);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                        } else {
+                            uint32_t pk[8];
+                            if (a.out_type == DT_BF16) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) { __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]); pk[j] = *reinterpret_cast<uint32_t*>(&h2); }
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) { __half2 h2 = __floats2half2_rn(v[2 * j], v[2 * j + 1]); pk[j] = *reinterpret_cast<uint32_t*>(&h2); }
+                            }
+                            uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(a.out) + m * a.ldo + n);
+                            o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                            o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                        }
+                    }
+                    if (a.out_t) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const size_t o = ot_base + (size_t)(n + j) * a.T;
+                            a.out_t[o] = v[j] + (a.res_t ? a.res_t[o] : 0.0f);
+                        }
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(&tempty[as]);
+            if (++as == 2) { as = 0; aphase ^= 1; }
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<C::TMEM_COLS>(tmem_base);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+
+}  // namespace
+
+struct TcGemmPlan {
+    CUtensorMap tmA, tmW;
+    TcGemmArgs args;
+    int block_n;
+    int grid;
+};
+
+const char* tc_init() {
+    if (g_encode) return nullptr;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return "cuTensorMapEncodeTiled not available from the driver";
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    cudaFuncSetAttribute(tc_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::SMEM_BYTES);
+    cudaFuncSetAttribute(tc_gemm_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::SMEM_BYTES);
+    cudaFuncSetAttribute(tc_gemm_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<80>::SMEM_BYTES);
+    if (cudaGetLastError() != cudaSuccess) return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
+    return nullptr;
+}
+
+TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** err) {
+    static thread_local char msg[256];
+    auto bad = [&](const char* m) -> TcGemmPlan* { if (err) *err = m; return nullptr; };
+    if (!g_encode) return bad("tc_init() not called");
+    if (p.a_type != p.w_type || (p.a_type != DT_BF16 && p.a_type != DT_F16)) return bad("operands must both be bf16 or both fp16");
+    if ((p.lda * 2) % 16 || (p.ldw * 2) % 16) return bad("row pitches must be multiples of 16 bytes");
+    if (p.out && ((p.ldo * dtype_size(p.out_type)) % 16)) return bad("output pitch must be a multiple of 16 bytes");
+    if (p.Cp % BLOCK_K) {
+        // plain GEMMs may have a ragged K tail: TMA zero-fills both operands beyond Kp
+        if (p.taps != 1) return bad("conv Cp must be a multiple of 64");
+    }
+    TcGemmPlan* plan = new TcGemmPlan();
+    TcGemmArgs& a = plan->args;
+    a.N = p.N; a.taps = p.taps; a.Cp = p.Cp; a.pad = p.taps / 2;
+    a.kblocks_per_tap = ceil_div(p.taps == 1 ? p.K : p.Cp, BLOCK_K);
+    a.T = p.T;
+    a.bias = p.bias; a.act = p.act; a.out = p.out; a.out_type = p.out_type; a.ldo = p.ldo; a.out_t = p.out_t; a.res_t = p.res_t;
+
+    // ---- M tiling: tile = BB utterances x TB frames, TB*BB = 128 ----
+    if (p.taps == 1) { a.gT = p.M; a.gB = 1; a.TB = BLOCK_M; a.BB = 1; }
+    else {
+        a.gT = p.T; a.gB = p.M / p.T;
+        long best = -1; int bestTB = BLOCK_M;
+        for (int TB = BLOCK_M; TB >= 8; TB >>= 1) {
+            const int BB = BLOCK_M / TB;
+            const long cost = (long)ceil_div(a.gT, TB) * TB * ceil_div(a.gB, BB) * BB;
+            if (best < 0 || cost < best) { best = cost; bestTB = TB; }
+        }
+        a.TB = bestTB; a.BB = BLOCK_M / bestTB;
+    }
+    a.tiles_t = ceil_div(a.gT, a.TB);
+    const int tiles_m = a.tiles_t * ceil_div(a.gB, a.BB);
+
+    // ---- N tiling ----
+    int bn;
+    if (p.N % 256 == 0 && (long)tiles_m * (p.N / 256) >= num_sms) bn = 256;
+    else if (p.N % 128 == 0) bn = 128;
+    else if (p.N == 80) bn = 80;
+    else { delete plan; snprintf(msg, sizeof msg, "N=%d is not a multiple of 128 (or 80)", p.N); return bad(msg); }
+    plan->block_n = bn;
+    a.tiles_n = p.N / bn;
+    a.num_tiles = tiles_m * a.tiles_n;
+    plan->grid = a.num_tiles < num_sms ? a.num_tiles : num_sms;
+    a.idesc = ptx::umma_idesc_f16(p.a_type == DT_BF16 ? 1 : 0, BLOCK_M, bn);
+
+    // ---- tensor maps ----
+    const CUtensorMapDataType dt = p.a_type == DT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    {
+        const cuuint64_t kdim = (cuuint64_t)(p.taps == 1 ? p.K : p.Cin);
+        cuuint64_t gdim[3] = {kdim, (cuuint64_t)a.gT, (cuuint64_t)a.gB};
+        cuuint64_t gstr[2] = {(cuuint64_t)p.lda * 2, (cuuint64_t)a.gT * p.lda * 2};
+        cuuint32_t box[3] = {(cuuint32_t)BLOCK_K, (cuuint32_t)a.TB, (cuuint32_t)a.BB};
+        cuuint32_t est[3] = {1, 1, 1};
+        CUresult r = g_encode(&plan->tmA, dt, 3, const_cast<void*>(p.A), gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(A) failed: %d", (int)r); return bad(msg); }
+    }
+    {
+        cuuint64_t gdim[2] = {(cuuint64_t)p.ldw, (cuuint64_t)p.N};
+        cuuint64_t gstr[1] = {(cuuint64_t)p.ldw * 2};
+        cuuint32_t box[2] = {(cuuint32_t)BLOCK_K, (cuuint32_t)bn};
+        cuuint32_t est[2] = {1, 1};
+        CUresult r = g_encode(&plan->tmW, dt, 2, const_cast<void*>(p.W), gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(W) failed: %d", (int)r); return bad(msg); }
+    }
+    return plan;
+}
+
+void tc_gemm_plan_destroy(TcGemmPlan* plan) { delete plan; }
+
+cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s) {
+    switch (plan->block_n) {
+        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->args); break;
+        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->args); break;
+        default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->args); break;
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace avc

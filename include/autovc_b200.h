@@ -1,0 +1,137 @@
+/*
+ * autovc_b200 - C ABI of the B200-native AutoVC generator forward pass.
+ *
+ * This is the drop-in boundary for ONE path of Fagprojekt-Deep-voice-conversion/AutoVC:
+ *     AutoEncoder.forward(x, c_org, c_trg) -> (mel_outputs, mel_outputs_postnet, content_codes)
+ *     reference: autovc/auto_encoder/model.py:68-146 (eval-mode BatchNorm, no_grad)
+ * and the encoder-only pass used by the content loss
+ *     AutoEncoder.forward(x, c_org, None)  -> content_codes        (model.py:98-101, model.py:201)
+ *
+ * The reference exposes a Python nn.Module, not an FFI; the entry points below are what a cffi /
+ * ctypes / pybind binding of that module would bind (see INTEGRATION.md for the stub).  Plain
+ * pointers and sizes only, no torch types; never throws across the ABI; every function returns
+ * AVC_OK (0) or a negative avc_status and records a message retrievable with avc_last_error().
+ *
+ * Threading: one handle per device; a handle is not re-entrant (it owns recurrent scratch state
+ * inside the caller's workspace).  All work is enqueued on the caller's stream, there is no
+ * hidden synchronisation in avc_forward()/avc_encode().
+ */
+#ifndef AUTOVC_B200_H
+#define AUTOVC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct avc_ctx* avc_handle;
+
+/* AutoEncoder ctor arguments, reference model.py:31-38 / utils/hparams.py:17-20 (32/256/512/32). */
+typedef struct avc_dims {
+    int32_t dim_neck; /* bottleneck width per direction            */
+    int32_t dim_emb;  /* speaker-embedding width                   */
+    int32_t dim_pre;  /* decoder pre-LSTM / conv width             */
+    int32_t freq;     /* code sampling period in frames            */
+} avc_dims;
+
+typedef enum avc_status {
+    AVC_OK = 0,
+    AVC_ERR_INVALID_ARG = -1,  /* null pointer, bad dims, B<=0 ...                                  */
+    AVC_ERR_T_TOO_SHORT = -2,  /* T < freq: the reference raises ValueError in torch.cat */
+    AVC_ERR_CUDA = -3,         /* a CUDA runtime/driver call failed; message has the CUDA error string */
+    AVC_ERR_NOT_LOADED = -4,   /* forward before a complete avc_load_weights()                        */
+    AVC_ERR_WORKSPACE = -5,    /* workspace null / too small / misaligned                            */
+    AVC_ERR_MISSING_WEIGHT = -6, /* a state-dict entry is absent or has the wrong element count       */
+    AVC_ERR_UNSUPPORTED = -7   /* dims outside what the kernels support                              */
+} avc_status;
+
+typedef enum avc_precision {
+    AVC_PREC_BF16 = 0, /* tensor-core path: bf16 operands (fp16 in the tanh-bounded postnet), fp32 accumulate */
+    AVC_PREC_FP32 = 1  /* validation path: fp32 operands and accumulation on the CUDA cores                   */
+} avc_precision;
+
+/* One state-dict entry in the reference's own naming and layout (float32, contiguous, HOST memory),
+ * e.g. "encoder.convolutions.0.0.conv.weight" [512,336,5], "decoder.lstm2.weight_hh_l1" [4096,1024].
+ * Names are fixed by ConvNorm/LinearNorm (reference autovc/auto_encoder/net_layers.py:13,39).
+ * "*.num_batches_tracked" entries are ignored.  The data is copied; the caller keeps ownership. */
+typedef struct avc_weight_desc {
+    const char* name;
+    const float* data;
+    int64_t numel;
+} avc_weight_desc;
+
+/* Create a context on CUDA device `device` (>= 0).  device == -1 creates a HOST-ONLY context that can
+ * load + pack weights (for inspection with avc_debug_packed) but cannot run.  Replaces
+ * AutoEncoder.__init__ (model.py:31-64). */
+int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision);
+
+/* Hand over the full state dict (any order).  Folds eval-mode BatchNorm into the convolutions
+ * (w' = w*g/sqrt(var+1e-5), b' = (b-mean)*g/sqrt(var+1e-5)+beta), sums bias_ih+bias_hh, re-orders LSTM
+ * gate rows to unit-major (u*4+gate), re-orders conv weights to tap-major K, converts to the context's
+ * precision and uploads.  Replaces AutoEncoder.load / load_state_dict (model.py:149-156). */
+int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n);
+
+/* Bytes of device scratch avc_forward/avc_encode need for a (B,T) batch.  0 on error. */
+size_t avc_workspace_bytes(avc_handle h, int B, int T);
+
+/* AutoEncoder.forward (model.py:68-146).  All pointers are DEVICE pointers owned by the caller:
+ *   x        [B,80,T]  float32, channel-first, contiguous
+ *   c_org    [B,dim_emb], c_trg [B,dim_emb] float32
+ *   mel      [B,80,T], mel_post [B,80,T] float32 outputs
+ *   codes    [B, dim_neck*(floor(T/freq)+ceil(T/freq))] float32: all forward codes then all backward codes
+ *   workspace: >= avc_workspace_bytes(h,B,T) bytes, 256-byte aligned
+ *   stream   : cudaStream_t (as void*), may be 0 for the legacy default stream
+ * Returns AVC_ERR_T_TOO_SHORT when T < freq. */
+int avc_forward(avc_handle h, const float* x, const float* c_org, const float* c_trg, int B, int T,
+                float* mel, float* mel_post, float* codes, void* workspace, size_t workspace_bytes,
+                void* stream);
+
+/* AutoEncoder.forward(x, c_org, None) (model.py:98-101): encoder + code sampling only. */
+int avc_encode(avc_handle h, const float* x, const float* c_org, int B, int T, float* codes,
+               void* workspace, size_t workspace_bytes, void* stream);
+
+/* Number of kernel launches the last avc_forward/avc_encode enqueued (for bench.py's gpu_launches). */
+int64_t avc_last_launch_count(avc_handle h);
+
+/* Optional per-phase device timing of the NEXT runs: CUDA events are recorded on the caller's stream at phase
+ * boundaries; avc_get_profile() synchronises on the last one and returns the milliseconds spent per phase in the
+ * most recent run (ms must have room for AVC_PHASE_COUNT floats).  bench.py uses this for the roofline object. */
+typedef enum avc_phase {
+    AVC_PHASE_LAYOUT = 0,   /* input packing, code sampling                              */
+    AVC_PHASE_CONV = 1,     /* the 11 conv1d(k=5) implicit GEMMs                         */
+    AVC_PHASE_PROJ = 2,     /* hoisted LSTM input projections + the final linear layer   */
+    AVC_PHASE_ENC_LSTM = 3, /* encoder BiLSTM recurrences (2 layers x 2 directions)      */
+    AVC_PHASE_LSTM1 = 4,    /* decoder lstm1 recurrence                                  */
+    AVC_PHASE_LSTM2 = 5,    /* decoder lstm2 recurrences (2 layers)                      */
+    AVC_PHASE_COUNT = 6
+} avc_phase;
+int avc_set_profiling(avc_handle h, int enable);
+int avc_get_profile(avc_handle h, float* ms, int n);
+
+/* Copy a packed host-side weight blob for inspection (tests).  `which`: "<layer>.w" (float32 master
+ * of the packed [N,Kp] matrix) or "<layer>.b" (float32 bias); layer names are listed in DESIGN.md.
+ * Returns the element count (and copies min(count, cap) floats into out if out != NULL), or a
+ * negative avc_status. */
+int64_t avc_debug_packed(avc_handle h, const char* which, float* out, int64_t cap);
+
+/* Run ONE GEMM-shaped layer (conv / projection / linear, names as in avc_debug_packed) on caller-provided device
+ * buffers, on the tensor cores (use_tc != 0) or on the CUDA cores, for per-layer parity tests.
+ * a_type/out_type: 0 = float32, 1 = bfloat16, 2 = float16.  A is [M][lda] channel-last rows of T-frame utterances;
+ * out is [M][ldo] (nullable); out_t is the channel-first float32 [M/T][N][T] output (nullable) with optional residual. */
+int avc_debug_gemm(avc_handle h, const char* layer, int use_tc, const void* A, int a_type, int lda, int M, int T, int act,
+                   void* out, int out_type, int ldo, float* out_t, const float* res_t, void* stream);
+
+void avc_destroy(avc_handle h);
+
+/* Last error message of this handle (or of the failed avc_create when h == NULL). Never NULL. */
+const char* avc_last_error(avc_handle h);
+
+/* ABI version; bumped on any signature change. */
+int avc_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AUTOVC_B200_H */

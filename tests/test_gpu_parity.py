@@ -1,0 +1,150 @@
+"""Parity tests proper (need a B200): the CUDA path, called through the custom op / C ABI, against
+(1) the golden vectors generated from the unmodified reference, (2) the CPU oracle on the same seeded inputs,
+(3) size-independent properties at BASELINE.json's full sizes.
+
+Tolerances (north-star): fp32 validation mode max-abs <= 1e-4; bf16 mode max-abs(mel_outputs_postnet) <= 1e-2
+and cosine(codes) >= 0.999 per utterance."""
+import numpy as np
+import pytest
+import torch
+
+from autovc_b200.synth import synth_inputs, synth_state_dict
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-4
+BF16_POST_TOL = 1e-2
+BF16_COS = 0.999
+
+DEFAULT_CASES = ["synth_b2_t128", "synth_b2_t100", "synth_b1_t33", "synth_b1_t32", "synth_b5_t64_w3",
+                 "synth_b3_t400", "c1_samples_b2_t128"]
+
+
+def _model(precision, wseed=0, gain=1.0):
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cuda", verbose=False, precision=precision)
+    m.load_state_dict(synth_state_dict(wseed, recurrent_gain=gain))
+    return m
+
+
+_MODELS = {}
+
+
+def model(precision, wseed=0, gain=1.0):
+    key = (precision, wseed, gain)
+    if key not in _MODELS:
+        _MODELS[key] = _model(*key)
+    return _MODELS[key]
+
+
+def _case(name):
+    g = load_golden(name)
+    x, c_org, c_trg = synth_inputs(int(g["B"]), int(g["T"]), seed=int(g["xseed"]))
+    if "x" in g.files:
+        x = torch.from_numpy(g["x"])
+    return g, x.cuda(), c_org.cuda(), c_trg.cuda()
+
+
+@pytest.mark.parametrize("name", DEFAULT_CASES + ["stress_b2_t128_gain2p5"])
+def test_fp32_mode_matches_reference_golden(name):
+    g, x, c_org, c_trg = _case(name)
+    m = model("fp32", int(g["wseed"]), float(g["gain"]))
+    mel, post, codes = m(x, c_org, c_trg)
+    torch.cuda.synchronize()
+    assert mel.shape == x.shape and post.shape == x.shape and codes.shape == g["codes"].shape
+    assert float((mel.cpu() - torch.from_numpy(g["mel"])).abs().max()) <= FP32_TOL
+    assert float((post.cpu() - torch.from_numpy(g["mel_post"])).abs().max()) <= FP32_TOL
+    assert float((codes.cpu() - torch.from_numpy(g["codes"])).abs().max()) <= FP32_TOL
+    only = m(x, c_org, None)
+    assert torch.equal(only, codes)
+
+
+@pytest.mark.parametrize("name", DEFAULT_CASES)
+def test_bf16_mode_matches_reference_golden(name):
+    g, x, c_org, c_trg = _case(name)
+    m = model("bf16", int(g["wseed"]), float(g["gain"]))
+    mel, post, codes = m(x, c_org, c_trg)
+    torch.cuda.synchronize()
+    err_mel = float((mel.cpu() - torch.from_numpy(g["mel"])).abs().max())
+    err_post = float((post.cpu() - torch.from_numpy(g["mel_post"])).abs().max())
+    cos = float(torch.nn.functional.cosine_similarity(codes.cpu(), torch.from_numpy(g["codes"]), dim=1).min())
+    print(f"{name}: bf16 mel {err_mel:.2e} post {err_post:.2e} cos {cos:.6f}")
+    assert err_post <= BF16_POST_TOL and err_mel <= BF16_POST_TOL and cos >= BF16_COS
+    only = m(x, c_org, None)
+    assert torch.equal(only, codes)
+
+
+def test_stress_weights_bf16_stays_close():
+    """Recurrent gain 2.5 pushes the gates into saturation; bf16 is outside the 1e-2 budget by design here
+    (precision) - just bound it so that a gross error is caught."""
+    g, x, c_org, c_trg = _case("stress_b2_t128_gain2p5")
+    m = model("bf16", int(g["wseed"]), float(g["gain"]))
+    mel, post, codes = m(x, c_org, c_trg)
+    assert float((post.cpu() - torch.from_numpy(g["mel_post"])).abs().max()) <= 0.25
+    assert float(torch.nn.functional.cosine_similarity(codes.cpu(), torch.from_numpy(g["codes"]), dim=1).min()) >= 0.99
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_t_shorter_than_freq_raises_value_error(precision):
+    m = model(precision)
+    x, c_org, c_trg = synth_inputs(1, 31)
+    with pytest.raises(ValueError):
+        m(x.cuda(), c_org.cuda(), c_trg.cuda())
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", FP32_TOL), ("bf16", BF16_POST_TOL)])
+def test_batch_forward_overlap_average_golden(precision, tol):
+    g = load_golden("batch_forward_m3_n128")
+    m = model(precision, int(g["wseed"]))
+    x, c_org, c_trg = synth_inputs(3, 128, seed=int(g["xseed"]))
+    out = m.batch_forward(x.cuda(), c_org[:1].cuda(), c_trg[:1].cuda(), overlap=0.5)
+    assert out.shape == (80, 256)
+    assert float((out.cpu() - torch.from_numpy(g["out"])).abs().max()) <= tol
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", FP32_TOL), ("bf16", BF16_POST_TOL)])
+def test_against_live_oracle_long_utterance(precision, tol):
+    """T=1024 (config 3's length; 4097 dependent recurrent steps), B=2, against the CPU oracle run here."""
+    from oracle import autovc_oracle as O
+    sd = synth_state_dict(0)
+    x, c_org, c_trg = synth_inputs(2, 1024, seed=21)
+    ref_mel, ref_post, ref_codes = O.generator_forward(sd, x, c_org, c_trg)
+    mel, post, codes = model(precision)(x.cuda(), c_org.cuda(), c_trg.cuda())
+    assert float((post.cpu() - ref_post).abs().max()) <= tol
+    assert float((mel.cpu() - ref_mel).abs().max()) <= tol
+    assert float(torch.nn.functional.cosine_similarity(codes.cpu(), ref_codes, dim=1).min()) >= BF16_COS
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_full_size_batch_rows_are_independent(precision):
+    """BASELINE config 2 (B=256,T=128): every utterance is independent, so rows computed inside the
+    big batch equal the same rows computed alone, and a sample of rows matches the oracle."""
+    from oracle import autovc_oracle as O
+    m = model(precision)
+    x, c_org, c_trg = synth_inputs(256, 128, seed=3)
+    mel, post, codes = m(x.cuda(), c_org.cuda(), c_trg.cuda())
+    rows = [0, 77, 255]
+    idx = torch.tensor(rows)
+    mel_s, post_s, codes_s = m(x[idx].cuda(), c_org[idx].cuda(), c_trg[idx].cuda())
+    assert float((post[idx.cuda()] - post_s).abs().max()) <= 1e-5
+    assert float((codes[idx.cuda()] - codes_s).abs().max()) <= 1e-5
+    ref_mel, ref_post, ref_codes = O.generator_forward(synth_state_dict(0), x[idx], c_org[idx], c_trg[idx])
+    tol = FP32_TOL if precision == "fp32" else BF16_POST_TOL
+    assert float((post_s.cpu() - ref_post).abs().max()) <= tol
+    assert torch.isfinite(post).all() and torch.isfinite(mel).all()
+
+
+def test_training_shape_forward_pair():
+    """BASELINE config 5's two passes (reference model.py:306 then :201) at a reduced batch: pass 1 forward(X,c,c),
+    pass 2 encoder-only on mel_outputs_postnet."""
+    from oracle import autovc_oracle as O
+    m = model("fp32")
+    x, c_org, _ = synth_inputs(4, 128, seed=8, same_speaker=True)
+    mel, post, codes = m(x.cuda(), c_org.cuda(), c_org.cuda())
+    codes2 = m(post, c_org.cuda(), None)
+    sd = synth_state_dict(0)
+    r_mel, r_post, r_codes = O.generator_forward(sd, x, c_org, c_org)
+    r_codes2 = O.generator_forward(sd, r_post, c_org, None)
+    assert float((codes2.cpu() - r_codes2).abs().max()) <= FP32_TOL
+    assert float((post.cpu() - r_post).abs().max()) <= FP32_TOL

@@ -1,0 +1,110 @@
+"""Host-side logic that needs no GPU: the C-ABI library loads and exports every declared symbol, weight
+folding/packing (done in C++ inside avc_load_weights, inspected through a host-only context), the module's
+state-dict contract, error behaviour."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from autovc_b200.synth import state_dict_spec, synth_state_dict
+from oracle import autovc_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol(built_lib):
+    header = open(os.path.join(ROOT, "include", "autovc_b200.h")).read()
+    declared = sorted(set(re.findall(r"\b(avc_[a-z_]+)\s*\(", header)))
+    assert len(declared) >= 10
+    lib = ctypes.CDLL(built_lib)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/autovc_b200.h but not exported"
+    assert lib.avc_abi_version() == 1
+
+
+def test_state_dict_contract():
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cpu", verbose=False)
+    keys = list(m.state_dict().keys())
+    assert keys == [n for n, _, _ in state_dict_spec()]
+    for (n, shape, _), (k, v) in zip(state_dict_spec(), m.state_dict().items()):
+        assert tuple(v.shape) == tuple(shape), n
+    assert sum(p.numel() for p in m.parameters()) == 28_422_464
+    assert m.encoder.freq == 32 and m.decoder.linear_projection.linear_layer.out_features == 80
+    assert not m.training
+
+
+@pytest.fixture(scope="module")
+def host_engine(built_lib):
+    from autovc_b200.engine import Engine
+    eng = Engine((32, 256, 512, 32), -1, "fp32")   # device -1: host-only context (pack, no run)
+    eng.load_state_dict(synth_state_dict(0))
+    yield eng
+    eng.close()
+
+
+def test_conv_bn_fold_and_tap_major_packing(host_engine):
+    sd = synth_state_dict(0)
+    p = "encoder.convolutions.0"
+    w, b = O.fold_batchnorm(sd[p + ".0.conv.weight"].double(), sd[p + ".0.conv.bias"].double(), sd[p + ".1.weight"].double(),
+                            sd[p + ".1.bias"].double(), sd[p + ".1.running_mean"].double(), sd[p + ".1.running_var"].double())
+    packed = host_engine.packed("enc.conv0.w").view(512, 5, 384)       # [Cout][tap][Cin padded to 384]
+    assert torch.allclose(packed[:, :, :336], w.permute(0, 2, 1).float(), atol=1e-7)
+    assert float(packed[:, :, 336:].abs().max()) == 0.0
+    assert torch.allclose(host_engine.packed("enc.conv0.b"), b.float(), atol=1e-7)
+    # postnet first layer: Cin 80 padded to 128
+    assert host_engine.packed("post.conv0.w").numel() == 512 * 5 * 128
+    assert host_engine.packed("post.conv4.w").numel() == 80 * 5 * 512
+
+
+def test_lstm_unit_major_gate_packing(host_engine):
+    sd = synth_state_dict(0)
+    H = 1024
+    whh = sd["decoder.lstm2.weight_hh_l1"]
+    packed = host_engine.packed("dec.lstm2.l1.hh.w").view(H, 4, H)     # row u*4+g <- torch row g*H+u
+    for g in range(4):
+        assert torch.equal(packed[:, g, :], whh[g * H:(g + 1) * H, :])
+    bias = host_engine.packed("dec.lstm2.l1.ih.b").view(H, 4)
+    full = sd["decoder.lstm2.bias_ih_l1"] + sd["decoder.lstm2.bias_hh_l1"]
+    assert torch.equal(bias[:, 2], full[2 * H:3 * H])
+    # bidirectional encoder: direction-major, then unit-major
+    wih = host_engine.packed("enc.lstm.l1.ih.w").view(2, 32, 4, 64)
+    assert torch.equal(wih[1, :, 3, :], sd["encoder.lstm.weight_ih_l1_reverse"][96:128, :])
+
+
+def test_missing_weight_is_reported(built_lib):
+    from autovc_b200.engine import Engine
+    eng = Engine((32, 256, 512, 32), -1, "bf16")
+    sd = synth_state_dict(0)
+    del sd["decoder.lstm1.weight_hh_l0"]
+    with pytest.raises(KeyError, match="decoder.lstm1.weight_hh_l0"):
+        eng.load_state_dict(sd)
+    eng.close()
+
+
+def test_unsupported_dims_and_host_only_run(built_lib):
+    from autovc_b200.engine import Engine
+    with pytest.raises(RuntimeError, match="dim_neck"):
+        Engine((30, 256, 512, 32), -1, "bf16")
+    eng = Engine((32, 256, 512, 32), -1, "bf16")
+    assert eng.workspace_bytes(256, 128) > 0
+    eng.close()
+
+
+def test_no_cpu_fallback():
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cpu", verbose=False)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m(torch.zeros(1, 80, 64), torch.zeros(1, 256), torch.zeros(1, 256))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        torch.ops.autovc_b200.generator_encode(torch.zeros(1, 80, 64), torch.zeros(1, 256), 1)
+
+
+def test_overlap_average_matches_oracle():
+    import autovc_b200
+    x = torch.randn(4, 80, 64)
+    assert torch.allclose(autovc_b200.overlap_average(x, 0.5), O.overlap_average(x, 0.5))
+    assert autovc_b200.overlap_average(x, 0.25).shape == (80, 64 + 3 * 48)
