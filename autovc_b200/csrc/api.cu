@@ -54,6 +54,7 @@ struct Workspace {
     // all pointers are carved from the caller's workspace; sizes in bytes
     char* X0; char* actA; char* actB; float* GxE; char* Y0; float* Y1; float* cstate;
     char* Dm; float* Gd1; char* H1; float* G2; char* H2a; char* H2b; char* melc;
+    unsigned int* ready; size_t ready_bytes;
     size_t total;
 };
 
@@ -72,6 +73,8 @@ struct avc_ctx {
     int64_t launches = 0;
     // tensor-core plan cache (valid for one (B,T,workspace) triple)
     std::vector<TcGemmPlan*> plans;
+    std::vector<TcLstmPlan*> lplans;
+    bool simt_lstm = false;    // AVC_SIMT_LSTM=1: debugging aid, per-step CUDA-core recurrences in the bf16 mode
     int plan_B = 0, plan_T = 0;
     void* plan_ws = nullptr;
     bool plan_encode_only = false;
@@ -233,6 +236,8 @@ Workspace carve(const avc_ctx* h, char* base, int B, int T) {
     w.H2a = take(M * LSTM2_H * as);
     w.H2b = take(M * LSTM2_H * as);
     w.melc = take(M * N_MELS * as);
+    w.ready_bytes = (size_t)tc_lstm_ready_words(B, T) * 4;
+    w.ready = (unsigned int*)take(w.ready_bytes);
     w.total = off;
     return w;
 }
@@ -245,7 +250,7 @@ struct Runner {
     cudaStream_t s;
     int B, T;
     int rc = AVC_OK;
-    size_t plan_cursor = 0;
+    size_t plan_cursor = 0, lplan_cursor = 0;
     bool building_plans = false;
 
     bool ok() const { return rc == AVC_OK; }
@@ -302,6 +307,20 @@ struct Runner {
         const Layer& L = h->layers[lid_hh];
         mark(lid_hh <= L_ENC_L1_HH ? AVC_PHASE_ENC_LSTM : (lid_hh == L_DEC_LSTM1_HH ? AVC_PHASE_LSTM1 : AVC_PHASE_LSTM2));
         const size_t hs = dtype_size(h_type);
+        if (use_tc() && !h->simt_lstm && ndir == 1 && h_type == DT_BF16 && L.w_type == DT_BF16 && H % 64 == 0) {
+            // persistent tensor-core recurrence (tc_lstm.cu)
+            if (building_plans) {
+                const char* why = nullptr;
+                TcLstmPlan* plan = tc_lstm_plan_create(L.w_dev, Gx, Tg, gx_div, Y, wsp->ready, B, T, H, h->num_sms, &why);
+                if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core LSTM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
+                h->lplans.push_back(plan);
+            }
+            check(cudaMemsetAsync(wsp->ready, 0, wsp->ready_bytes, s), "memset step counters");
+            int n = 0;
+            check(launch_tc_lstm(h->lplans[lplan_cursor++], s, &n), L.name.c_str());
+            h->launches += n;
+            return;
+        }
         check(cudaMemsetAsync(wsp->cstate, 0, (size_t)2 * B * H * 4, s), "memset c");
         const int ldy = ndir * H;
         for (int step = 0; step < T && ok(); ++step) {
@@ -350,6 +369,8 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         if (!hit) {
             for (auto* p : h->plans) tc_gemm_plan_destroy(p);
             h->plans.clear();
+            for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
+            h->lplans.clear();
             r.building_plans = true;
             h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_encode_only = encode_only;
         }
@@ -398,6 +419,8 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     if (!r.ok() && r.building_plans) {  // do not keep a half-built plan set
         for (auto* p : h->plans) tc_gemm_plan_destroy(p);
         h->plans.clear();
+        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
+        h->lplans.clear();
         h->plan_ws = nullptr;
     }
     return r.rc;
@@ -427,6 +450,8 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
     h->dims = *dims; h->device = device; h->precision = precision;
     const char* fs = getenv("AVC_FORCE_SIMT");
     h->force_simt = fs && fs[0] == '1';
+    const char* sl = getenv("AVC_SIMT_LSTM");
+    h->simt_lstm = sl && sl[0] == '1';
     for (int i = 0; i < L_COUNT; ++i) h->layers[i].name = kLayerNames[i];
     if (device >= 0) {
         cudaError_t e = cudaSetDevice(device);
@@ -437,7 +462,8 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
         h->num_sms = prop.multiProcessorCount;
         if (precision == AVC_PREC_BF16 && !h->force_simt) {
             const char* why = tc_init();
-            if (why) { int rc = fail(nullptr, AVC_ERR_CUDA, "tensor-map driver entry point: %s", why); delete h; return rc; }
+            if (!why) why = tc_lstm_init();
+            if (why) { int rc = fail(nullptr, AVC_ERR_CUDA, "tensor-core kernel setup: %s", why); delete h; return rc; }
         }
     }
     *out = h;
@@ -488,6 +514,8 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
         }
         for (auto* p : h->plans) tc_gemm_plan_destroy(p);
         h->plans.clear();
+        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
+        h->lplans.clear();
         h->plan_ws = nullptr;
     }
     h->loaded = true;
@@ -584,6 +612,7 @@ void avc_destroy(avc_handle h) {
             if (h->layers[i].b_dev) cudaFree(h->layers[i].b_dev);
         }
         for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
         for (auto ev : h->prof_events) cudaEventDestroy(ev);
     }
     delete h;

@@ -21,4 +21,13 @@ cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s);
 // one-time driver entry point lookup; returns nullptr on success or an error string
 const char* tc_init();
 
+// tc_lstm.cu (persistent weight-stationary LSTM recurrence, tcgen05 + TMA + global step counters)
+struct TcLstmPlan;
+const char* tc_lstm_init();
+TcLstmPlan* tc_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, unsigned int* ready,
+                                int B, int T, int H, int num_sms, const char** err);
+void tc_lstm_plan_destroy(TcLstmPlan* plan);
+int tc_lstm_ready_words(int B, int T);
+cudaError_t launch_tc_lstm(const TcLstmPlan* plan, cudaStream_t s, int* launches);
+
 }  // namespace avc
