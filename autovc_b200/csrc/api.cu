@@ -388,12 +388,24 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     r.gemm(L_ENC_CONV1, w.actA, at, CONV_CH, M, T, ACT_RELU, w.actB, at, CONV_CH);
     r.gemm(L_ENC_CONV2, w.actB, at, CONV_CH, M, T, ACT_RELU, w.actA, at, CONV_CH);
     r.gemm(L_ENC_L0_IH, w.actA, at, CONV_CH, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
-    r.lstm(L_ENC_L0_HH, w.GxE, T, 1, w.Y0, at, dn, 2);
-    r.gemm(L_ENC_L1_IH, w.Y0, at, 2 * dn, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
-    r.lstm(L_ENC_L1_HH, w.GxE, T, 1, w.Y1, DT_F32, dn, 2);
-    // code sampling + de-duplicated decoder input (encoder.py:94-95, model.py:99-124)
-    r.mark(AVC_PHASE_LAYOUT);
-    r.check(launch_codes(w.Y1, c_trg, codes, encode_only ? nullptr : w.Dm, at, B, T, dn, E, d.freq, r.s), "codes"); h->launches++;
+    if (r.use_tc() && !h->simt_lstm && enc_lstm_supported(dn)) {
+        // register-resident BiLSTM kernels; layer 1 samples the codes and writes the decoder input itself
+        r.mark(AVC_PHASE_ENC_LSTM);
+        r.check(launch_enc_lstm_l0(w.GxE, h->layers[L_ENC_L0_HH].w_dev, w.Y0, B, T, r.s), "enc lstm l0"); h->launches++;
+        r.gemm(L_ENC_L1_IH, w.Y0, at, 2 * dn, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
+        r.mark(AVC_PHASE_ENC_LSTM);
+        int n = 0;
+        r.check(launch_enc_lstm_l1(w.GxE, h->layers[L_ENC_L1_HH].w_dev, codes, w.Dm, 2 * dn + E, encode_only ? nullptr : c_trg, E,
+                                   B, T, d.freq, r.s, &n), "enc lstm l1");
+        h->launches += n;
+    } else {
+        r.lstm(L_ENC_L0_HH, w.GxE, T, 1, w.Y0, at, dn, 2);
+        r.gemm(L_ENC_L1_IH, w.Y0, at, 2 * dn, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
+        r.lstm(L_ENC_L1_HH, w.GxE, T, 1, w.Y1, DT_F32, dn, 2);
+        // code sampling + de-duplicated decoder input (encoder.py:94-95, model.py:99-124)
+        r.mark(AVC_PHASE_LAYOUT);
+        r.check(launch_codes(w.Y1, c_trg, codes, encode_only ? nullptr : w.Dm, at, B, T, dn, E, d.freq, r.s), "codes"); h->launches++;
+    }
 
     if (!encode_only) {
         // ---- decoder (reference decoder.py:58-79) ----

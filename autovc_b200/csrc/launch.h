@@ -30,4 +30,10 @@ void tc_lstm_plan_destroy(TcLstmPlan* plan);
 int tc_lstm_ready_words(int B, int T);
 cudaError_t launch_tc_lstm(const TcLstmPlan* plan, cudaStream_t s, int* launches);
 
+// enc_lstm.cu (encoder BiLSTM, H=32: one warp per 16 utterances x direction, W_hh in registers, mma.sync)
+bool enc_lstm_supported(int dim_neck);
+cudaError_t launch_enc_lstm_l0(const float* Gx, const void* Whh_bf16, void* Y_bf16, int B, int T, cudaStream_t s);
+cudaError_t launch_enc_lstm_l1(const float* Gx, const void* Whh_bf16, float* codes, void* D_bf16, int ldd, const float* c_trg,
+                               int E, int B, int T, int freq, cudaStream_t s, int* launches);
+
 }  // namespace avc
