@@ -55,6 +55,7 @@ struct Workspace {
     char* X0; char* actA; char* actB; float* GxE; char* Y0; float* Y1; float* cstate;
     char* Dm; float* Gd1; char* H1; float* G2; char* H2a; char* H2b; char* melc;
     unsigned int* ready; size_t ready_bytes;
+    char* Yb;    // recurrent operand-tile copy of the running LSTM layer's output (tc_lstm.cu)
     size_t total;
 };
 
@@ -238,6 +239,7 @@ Workspace carve(const avc_ctx* h, char* base, int B, int T) {
     w.melc = take(M * N_MELS * as);
     w.ready_bytes = (size_t)tc_lstm_ready_words(B, T) * 4;
     w.ready = (unsigned int*)take(w.ready_bytes);
+    w.Yb = take(tc_lstm_tile_bytes(B, T, hmax));
     w.total = off;
     return w;
 }
@@ -293,7 +295,7 @@ struct Runner {
                 if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core GEMM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
                 h->plans.push_back(plan);
             }
-            check(launch_tc_gemm(h->plans[plan_cursor++], s), L.name.c_str());
+            check(launch_tc_gemm(h->plans[plan_cursor++], s, out_t, res_t), L.name.c_str());
         } else {
             check(launch_simt_gemm(p, s), L.name.c_str());
         }
@@ -311,7 +313,7 @@ struct Runner {
             // persistent tensor-core recurrence (tc_lstm.cu)
             if (building_plans) {
                 const char* why = nullptr;
-                TcLstmPlan* plan = tc_lstm_plan_create(L.w_dev, Gx, Tg, gx_div, Y, wsp->ready, B, T, H, h->num_sms, &why);
+                TcLstmPlan* plan = tc_lstm_plan_create(L.w_dev, Gx, Tg, gx_div, Y, wsp->Yb, wsp->ready, B, T, H, h->num_sms, getenv("AVC_LSTM_TM_EXPERIMENT") != nullptr, &why);
                 if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core LSTM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
                 h->lplans.push_back(plan);
             }
@@ -604,7 +606,7 @@ int avc_debug_gemm(avc_handle h, const char* layer, int use_tc, const void* A, i
             if (why) return fail(h, AVC_ERR_CUDA, "%s", why);
             TcGemmPlan* plan = tc_gemm_plan_create(p, h->num_sms, &why);
             if (!plan) return fail(h, AVC_ERR_UNSUPPORTED, "tensor-core GEMM plan for %s: %s", layer, why ? why : "?");
-            e = launch_tc_gemm(plan, (cudaStream_t)stream);
+            e = launch_tc_gemm(plan, (cudaStream_t)stream, out_t, res_t);
             tc_gemm_plan_destroy(plan);   // tensor maps are passed by value at launch
         } else {
             e = launch_simt_gemm(p, (cudaStream_t)stream);

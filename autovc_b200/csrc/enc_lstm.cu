@@ -1,14 +1,14 @@
 // Encoder BiLSTM recurrence (reference encoder.py:51,74-77: nn.LSTM(512, 32, 2, bidirectional)), H = 32.
 //
 // The recurrent matrix is tiny (128 x 32 per direction), the chains (utterance x direction) are independent, so
-// there is nothing to exchange between CTAs: one WARP owns 16 utterances of one direction for the whole sequence.
+// there is nothing to exchange between CTAs: one WARP owns 8 utterances of one direction for the whole sequence.
 // W_hh lives in registers as mma.sync B fragments (64 registers), the cell state and h stay in registers, and the
 // unit/gate permutation below makes the accumulator fragment of step t exactly the A fragment of step t+1, so a
 // step is 32 HMMA + the gate math with no shuffle, no shared memory and no barrier.
 //
-//   D tile j (8 columns), thread (g = lane/4, q = lane%4) holds columns 2q,2q+1 for rows g and g+8
+//   D tile j (8 columns), thread (g = lane/4, q = lane%4) holds columns 2q,2q+1 for row g (rows 8..15 unused)
 //   column c of tile j  <->  unit (c/2)*8 + j/2, gate (j%2)*2 + c%2        => thread q owns units q*8 .. q*8+7,
-//   K position (s, kl)  <->  unit (kl%8/2)*8 + 4s + (kl/8)*2 + kl%2           all four gates, rows g and g+8
+//   K position (s, kl)  <->  unit (kl%8/2)*8 + 4s + (kl/8)*2 + kl%2           all four gates, row g
 //
 // Layer 1 also performs the reference's code sampling (encoder.py:94-95) and writes the de-duplicated decoder
 // input (model.py:115-124) directly: forward h at t = 31 mod 32, backward h at t = 0 mod 32, in fp32.
@@ -46,13 +46,15 @@ struct EncLstmArgs {
     int B, T, freq;
 };
 
+// One warp = 8 utterances (rows g = lane/4 of the m16 tile; rows 8..15 stay zero: the chains are latency-bound, so
+// halving the per-thread gate math is worth more than filling the tile) of one direction.
 template <bool kCodes>
 __global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
     const int lane = threadIdx.x;
     const int g = lane >> 2, q = lane & 3;
     const int dir = blockIdx.y;
-    const int b_lo = blockIdx.x * 16 + g, b_hi = b_lo + 8;
-    const bool ok_lo = b_lo < a.B, ok_hi = b_hi < a.B;
+    const int b = blockIdx.x * 8 + g;
+    const bool ok = b < a.B;
 
     // resident B fragments: tile j, k-step s -> W[row(j, g)][q*8 + 4s .. +3]
     uint32_t wb[16][2][2];
@@ -69,10 +71,10 @@ __global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
         }
     }
 
-    float c_lo[8], c_hi[8];
-    uint32_t af[2][4];                       // A fragments of h_{t-1} for the two k-steps
+    float c[8];
+    uint32_t af[2][4];                       // A fragments of h_{t-1} for the two k-steps (a1, a3 = rows 8..15 = 0)
 #pragma unroll
-    for (int w = 0; w < 8; ++w) { c_lo[w] = 0.f; c_hi[w] = 0.f; }
+    for (int w = 0; w < 8; ++w) c[w] = 0.f;
 #pragma unroll
     for (int s = 0; s < 2; ++s)
 #pragma unroll
@@ -80,19 +82,30 @@ __global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
 
     const int nf = a.T / a.freq, nb = (a.T + a.freq - 1) / a.freq;
     const size_t gx_pitch = (size_t)a.T * 8 * EH;            // floats per utterance
-    const float* gx_lo = a.Gx + (size_t)(ok_lo ? b_lo : 0) * gx_pitch + dir * 4 * EH + q * 32;
-    const float* gx_hi = a.Gx + (size_t)(ok_hi ? b_hi : 0) * gx_pitch + dir * 4 * EH + q * 32;
+    const float* gx = a.Gx + (size_t)(ok ? b : 0) * gx_pitch + dir * 4 * EH + q * 32;
+
+    // software pipeline: the hoisted input projection of step+1 is in flight while step is computed
+    float4 x_next[8];
+    {
+        const int t0 = dir == 0 ? 0 : a.T - 1;
+        const float4* p = reinterpret_cast<const float4*>(gx + (size_t)t0 * 8 * EH);
+#pragma unroll
+        for (int w = 0; w < 8; ++w) x_next[w] = __ldg(p + w);
+    }
 
     for (int step = 0; step < a.T; ++step) {
         const int t = dir == 0 ? step : a.T - 1 - step;
-        // hoisted input projection: 8 units x 4 gates per row, contiguous 128 bytes per row
-        float4 x_lo[8], x_hi[8];
-        const float4* pl = reinterpret_cast<const float4*>(gx_lo + (size_t)t * 8 * EH);
-        const float4* ph = reinterpret_cast<const float4*>(gx_hi + (size_t)t * 8 * EH);
+        float4 x[8];
 #pragma unroll
-        for (int w = 0; w < 8; ++w) { x_lo[w] = __ldg(pl + w); x_hi[w] = __ldg(ph + w); }
+        for (int w = 0; w < 8; ++w) x[w] = x_next[w];
+        if (step + 1 < a.T) {
+            const int tn = dir == 0 ? t + 1 : t - 1;
+            const float4* p = reinterpret_cast<const float4*>(gx + (size_t)tn * 8 * EH);
+#pragma unroll
+            for (int w = 0; w < 8; ++w) x_next[w] = __ldg(p + w);
+        }
 
-        float h_lo[8], h_hi[8];
+        float h[8];
 #pragma unroll
         for (int w = 0; w < 8; ++w) {
             // tiles 2w (i,f) and 2w+1 (g,o) of unit q*8+w
@@ -102,59 +115,35 @@ __global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
                 mma_bf16_16816(d_if, af[s], wb[2 * w][s][0], wb[2 * w][s][1]);
                 mma_bf16_16816(d_go, af[s], wb[2 * w + 1][s][0], wb[2 * w + 1][s][1]);
             }
-            {
-                const float ig = fast_sigmoid(d_if[0] + x_lo[w].x), fg = fast_sigmoid(d_if[1] + x_lo[w].y);
-                const float gg = fast_tanh(d_go[0] + x_lo[w].z), og = fast_sigmoid(d_go[1] + x_lo[w].w);
-                c_lo[w] = fg * c_lo[w] + ig * gg;
-                h_lo[w] = og * fast_tanh(c_lo[w]);
-            }
-            {
-                const float ig = fast_sigmoid(d_if[2] + x_hi[w].x), fg = fast_sigmoid(d_if[3] + x_hi[w].y);
-                const float gg = fast_tanh(d_go[2] + x_hi[w].z), og = fast_sigmoid(d_go[3] + x_hi[w].w);
-                c_hi[w] = fg * c_hi[w] + ig * gg;
-                h_hi[w] = og * fast_tanh(c_hi[w]);
-            }
+            const float ig = fast_sigmoid(d_if[0] + x[w].x), fg = fast_sigmoid(d_if[1] + x[w].y);
+            const float gg = fast_tanh(d_go[0] + x[w].z), og = fast_sigmoid(d_go[1] + x[w].w);
+            c[w] = fg * c[w] + ig * gg;
+            h[w] = og * fast_tanh(c[w]);
         }
-        // next step's A fragments: k-step s, a0/a2 = row g units (4s, 4s+1)/(4s+2, 4s+3); a1/a3 = row g+8
+        // next step's A fragments: k-step s, a0 = units (4s, 4s+1), a2 = units (4s+2, 4s+3) of row g
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-            af[s][0] = pack_bf16(h_lo[4 * s + 0], h_lo[4 * s + 1]);
-            af[s][1] = pack_bf16(h_hi[4 * s + 0], h_hi[4 * s + 1]);
-            af[s][2] = pack_bf16(h_lo[4 * s + 2], h_lo[4 * s + 3]);
-            af[s][3] = pack_bf16(h_hi[4 * s + 2], h_hi[4 * s + 3]);
+            af[s][0] = pack_bf16(h[4 * s + 0], h[4 * s + 1]);
+            af[s][2] = pack_bf16(h[4 * s + 2], h[4 * s + 3]);
         }
+        const uint4 v = make_uint4(af[0][0], af[0][2], af[1][0], af[1][2]);
         if constexpr (!kCodes) {
             // layer 0: h_t (bf16) -> Y[b][t][dir*32 + q*8 .. +7]
-            const uint4 v_lo = make_uint4(af[0][0], af[0][2], af[1][0], af[1][2]);
-            const uint4 v_hi = make_uint4(af[0][1], af[0][3], af[1][1], af[1][3]);
-            if (ok_lo) *reinterpret_cast<uint4*>(a.Y + ((size_t)b_lo * a.T + t) * (2 * EH) + dir * EH + q * 8) = v_lo;
-            if (ok_hi) *reinterpret_cast<uint4*>(a.Y + ((size_t)b_hi * a.T + t) * (2 * EH) + dir * EH + q * 8) = v_hi;
+            if (ok) *reinterpret_cast<uint4*>(a.Y + ((size_t)b * a.T + t) * (2 * EH) + dir * EH + q * 8) = v;
         } else {
             // layer 1: code sampling (fp32) + de-duplicated decoder input (bf16)
             const bool hit = dir == 0 ? (t % a.freq == a.freq - 1) : (t % a.freq == 0);
-            if (hit) {
+            if (hit && ok) {
                 const int j = t / a.freq;
                 const size_t cl = (size_t)EH * (nf + nb);
                 const size_t coff = (dir == 0 ? (size_t)j * EH : (size_t)(nf + j) * EH) + q * 8;
-                const uint4 v_lo = make_uint4(af[0][0], af[0][2], af[1][0], af[1][2]);
-                const uint4 v_hi = make_uint4(af[0][1], af[0][3], af[1][1], af[1][3]);
-                if (ok_lo) {
-                    float4* cp = reinterpret_cast<float4*>(a.codes + (size_t)b_lo * cl + coff);
-                    cp[0] = make_float4(h_lo[0], h_lo[1], h_lo[2], h_lo[3]);
-                    cp[1] = make_float4(h_lo[4], h_lo[5], h_lo[6], h_lo[7]);
-                    __nv_bfloat16* dp = a.D + ((size_t)b_lo * nb + j) * a.ldd + dir * EH + q * 8;
-                    *reinterpret_cast<uint4*>(dp) = v_lo;
-                    // the tail segment (t >= freq*nf) repeats the LAST forward code (reference model.py:116-117)
-                    if (dir == 0 && j == nf - 1 && nb > nf) *reinterpret_cast<uint4*>(dp + a.ldd) = v_lo;
-                }
-                if (ok_hi) {
-                    float4* cp = reinterpret_cast<float4*>(a.codes + (size_t)b_hi * cl + coff);
-                    cp[0] = make_float4(h_hi[0], h_hi[1], h_hi[2], h_hi[3]);
-                    cp[1] = make_float4(h_hi[4], h_hi[5], h_hi[6], h_hi[7]);
-                    __nv_bfloat16* dp = a.D + ((size_t)b_hi * nb + j) * a.ldd + dir * EH + q * 8;
-                    *reinterpret_cast<uint4*>(dp) = v_hi;
-                    if (dir == 0 && j == nf - 1 && nb > nf) *reinterpret_cast<uint4*>(dp + a.ldd) = v_hi;
-                }
+                float4* cp = reinterpret_cast<float4*>(a.codes + (size_t)b * cl + coff);
+                cp[0] = make_float4(h[0], h[1], h[2], h[3]);
+                cp[1] = make_float4(h[4], h[5], h[6], h[7]);
+                __nv_bfloat16* dp = a.D + ((size_t)b * nb + j) * a.ldd + dir * EH + q * 8;
+                *reinterpret_cast<uint4*>(dp) = v;
+                // the tail segment (t >= freq*nf) repeats the LAST forward code (reference model.py:116-117)
+                if (dir == 0 && j == nf - 1 && nb > nf) *reinterpret_cast<uint4*>(dp + a.ldd) = v;
             }
         }
     }
@@ -176,7 +165,7 @@ bool enc_lstm_supported(int dim_neck) { return dim_neck == EH; }
 cudaError_t launch_enc_lstm_l0(const float* Gx, const void* Whh_bf16, void* Y_bf16, int B, int T, cudaStream_t s) {
     EncLstmArgs a{};
     a.Gx = Gx; a.Whh = (const __nv_bfloat16*)Whh_bf16; a.Y = (__nv_bfloat16*)Y_bf16; a.B = B; a.T = T; a.freq = 1;
-    enc_lstm_kernel<false><<<dim3(ceil_div(B, 16), 2), 32, 0, s>>>(a);
+    enc_lstm_kernel<false><<<dim3(ceil_div(B, 8), 2), 32, 0, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -191,7 +180,7 @@ cudaError_t launch_enc_lstm_l1(const float* Gx, const void* Whh_bf16, float* cod
         fill_speaker_kernel<<<B, 256, 0, s>>>(c_trg, a.D, nb, ldd, 2 * EH, E);
         if (launches) ++*launches;
     }
-    enc_lstm_kernel<true><<<dim3(ceil_div(B, 16), 2), 32, 0, s>>>(a);
+    enc_lstm_kernel<true><<<dim3(ceil_div(B, 8), 2), 32, 0, s>>>(a);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

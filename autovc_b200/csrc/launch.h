@@ -17,15 +17,17 @@ struct TcGemmPlan;  // opaque: tensor maps + tiling for one (layer, B, T) instan
 // Returns nullptr and sets *err when the shape is not supported by the tensor-core kernel.
 TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** err);
 void tc_gemm_plan_destroy(TcGemmPlan* plan);
-cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s);
+// out_t/res_t are the caller-owned channel-first output / residual of THIS call (never cached in the plan)
+cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t, const float* res_t);
 // one-time driver entry point lookup; returns nullptr on success or an error string
 const char* tc_init();
 
 // tc_lstm.cu (persistent weight-stationary LSTM recurrence, tcgen05 + TMA + global step counters)
 struct TcLstmPlan;
 const char* tc_lstm_init();
-TcLstmPlan* tc_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, unsigned int* ready,
-                                int B, int T, int H, int num_sms, const char** err);
+size_t tc_lstm_tile_bytes(int B, int T, int H);
+TcLstmPlan* tc_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, void* Yb, unsigned int* ready,
+                                int B, int T, int H, int num_sms, bool time_major, const char** err);
 void tc_lstm_plan_destroy(TcLstmPlan* plan);
 int tc_lstm_ready_words(int B, int T);
 cudaError_t launch_tc_lstm(const TcLstmPlan* plan, cudaStream_t s, int* launches);

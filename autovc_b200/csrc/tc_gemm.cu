@@ -317,11 +317,15 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
 
 void tc_gemm_plan_destroy(TcGemmPlan* plan) { delete plan; }
 
-cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s) {
+cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t, const float* res_t) {
+    // the cached plan owns only workspace/weight addresses; caller-owned output pointers are per call
+    TcGemmArgs args = plan->args;
+    args.out_t = out_t;
+    args.res_t = res_t;
     switch (plan->block_n) {
-        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->args); break;
-        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->args); break;
-        default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->args); break;
+        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, args); break;
+        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, args); break;
+        default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, args); break;
     }
     return cudaGetLastError();
 }

@@ -148,3 +148,15 @@ def test_training_shape_forward_pair():
     r_codes2 = O.generator_forward(sd, r_post, c_org, None)
     assert float((codes2.cpu() - r_codes2).abs().max()) <= FP32_TOL
     assert float((post.cpu() - r_post).abs().max()) <= FP32_TOL
+
+
+def test_outputs_do_not_alias_cached_plans():
+    """The plan cache holds workspace addresses only: fresh output tensors of later calls must be written even when
+    earlier outputs are still alive (regression: channel-first output pointers were once cached in the GEMM plans)."""
+    m = model("bf16")
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(2, 128, seed=1234))
+    keep = [m(x, c_org, c_trg) for _ in range(3)]       # all outputs alive -> three distinct allocations
+    torch.cuda.synchronize()
+    for mel, post, codes in keep[1:]:
+        assert torch.equal(post, keep[0][1]) and torch.equal(mel, keep[0][0]) and torch.equal(codes, keep[0][2])
+    assert float(keep[2][1].abs().max()) > 1.0
