@@ -1,0 +1,232 @@
+"""Batched conversion around the generator: the mel-level part of the reference's `VoiceConverter.convert` /
+`convert_multiple` (reference `autovc/voice_converter.py:88-211`, `:346-398`), re-designed for throughput:
+
+* the reference converts one (source, target) pair per `forward` call in a Python loop (`:391-392`, B = 1) and re-embeds
+  the target for every pair unless it is a cached key (`:150-155`); here every speaker is embedded ONCE and cached like
+  `SpeakerEncoder.speakers` (`speaker_encoder/model.py:101,446-460`), utterances are bucketed by frame count and each
+  bucket is one batched `AutoEncoder.forward`;
+* utterances are never padded across different lengths - the reference has no length masking, so padding would change
+  the BiLSTM result;
+* under `torch.distributed` every rank converts a contiguous block of the work list with replicated weights and no
+  collective on the data path; an optional final `all_gather_object` returns the complete list on every rank.
+
+Audio I/O, the mel front-end and the vocoder are outside this path: inputs are normalised mels
+`(80, T)`, outputs are `mel_outputs_postnet` `(80, T)` exactly as `convert` hands them to the vocoder (`:170,:175`).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from itertools import product
+from typing import Callable, Dict, Hashable, Iterable, List, Optional, Sequence, Tuple, Union
+
+import torch
+
+from .model import overlap_average
+
+SpeakerRef = Union[Hashable, torch.Tensor]
+
+
+@dataclass
+class Utterance:
+    """A source (or target) utterance: its mel `(80, T)` and the key of its speaker."""
+    mel: torch.Tensor
+    speaker: Hashable
+    speaker_data: object = None      # whatever the embedder needs to embed this speaker (e.g. d-vector partials)
+
+
+def shard_range(n: int, rank: int, world: int) -> range:
+    """Contiguous block of ceil(n/world) items per rank (SURVEY.md 8e 'contiguous blocks of ceil(B/G) rows per GPU')."""
+    per = (n + world - 1) // world
+    return range(min(n, rank * per), min(n, (rank + 1) * per))
+
+
+def bucket_by_length(lengths: Sequence[int]) -> Dict[int, List[int]]:
+    """frame count -> indices, in first-seen order; equal-length utterances batch together, nothing is padded."""
+    buckets: Dict[int, List[int]] = {}
+    for i, t in enumerate(lengths):
+        buckets.setdefault(int(t), []).append(i)
+    return buckets
+
+
+def chunk_mel(mel: torch.Tensor, n_frames: int, overlap: float = 0.5) -> torch.Tensor:
+    """Cut `(80, T)` into `(M, 80, n_frames)` windows with hop int(n_frames*(1-overlap)) - the wire format
+    `batch_forward` expects (reference `model.py:395-437`; the reference's slicer is `spectrogram.py:248-311`).
+    Trailing frames that do not fill a whole window are left out (the reference pads there, outside this path)."""
+    T = mel.shape[-1]
+    if T < n_frames:
+        raise ValueError(f"utterance has {T} frames, fewer than one chunk of {n_frames}")
+    hop = int(n_frames * (1 - overlap))
+    starts = list(range(0, T - n_frames + 1, hop))
+    return torch.stack([mel[:, s:s + n_frames] for s in starts])
+
+
+class VoiceConverter:
+    """Mel-level drop-in for the conversion loop of the reference `VoiceConverter`.
+
+    `auto_encoder`  : an `autovc_b200.AutoEncoder` (or any callable with the same `forward` contract - tests inject the oracle)
+    `embed_speaker` : callable(speaker_data) -> (dim_emb,) tensor, the d-vector encoder; called once per speaker key
+    `max_batch`     : utterances per `forward` (config 2 uses 256 per GPU)
+    """
+
+    def __init__(self, auto_encoder, embed_speaker: Optional[Callable[[object], torch.Tensor]] = None,
+                 device: Optional[torch.device] = None, max_batch: int = 256):
+        self.AE = auto_encoder
+        self.embed_speaker = embed_speaker
+        self.device = torch.device(device) if device is not None else getattr(auto_encoder, "device", torch.device("cpu"))
+        self.max_batch = int(max_batch)
+        self.speakers: Dict[Hashable, torch.Tensor] = {}
+        self.embed_calls = 0
+
+    # -- speakers ----------------------------------------------------------------------------------
+    def learn_speaker(self, key: Hashable, embedding: torch.Tensor) -> None:
+        """Register a (mean) speaker embedding under a key, like `SpeakerEncoder.learn_speaker` fills `.speakers`."""
+        self.speakers[key] = embedding.detach().to(torch.float32).reshape(-1).cpu()
+
+    def embedding(self, ref: SpeakerRef, data: object = None) -> torch.Tensor:
+        """Embedding of a speaker: a tensor is used as is, a known key hits the cache (reference `:150-151`), an
+        unknown key is embedded once from `data` and cached."""
+        if isinstance(ref, torch.Tensor):
+            return ref.detach().to(torch.float32).reshape(-1).cpu()
+        if ref in self.speakers:
+            return self.speakers[ref]
+        if self.embed_speaker is None or data is None:
+            raise KeyError(f"unknown speaker {ref!r} and nothing to embed it from")
+        self.embed_calls += 1
+        self.learn_speaker(ref, self.embed_speaker(data))
+        return self.speakers[ref]
+
+    # -- core: batched forward over a work list ----------------------------------------------------
+    def convert_batch(self, mels: Sequence[torch.Tensor], c_src: Sequence[torch.Tensor], c_trg: Sequence[torch.Tensor]):
+        """[(80,T_i)], [(E,)], [(E,)] -> [mel_outputs_postnet (80,T_i)] in input order.  One forward per
+        (length bucket, chunk of max_batch)."""
+        out: List[Optional[torch.Tensor]] = [None] * len(mels)
+        for T, idx in bucket_by_length([m.shape[-1] for m in mels]).items():
+            for s in range(0, len(idx), self.max_batch):
+                sel = idx[s:s + self.max_batch]
+                x = torch.stack([mels[i] for i in sel]).to(self.device, torch.float32)
+                co = torch.stack([c_src[i] for i in sel]).to(self.device, torch.float32)
+                ct = torch.stack([c_trg[i] for i in sel]).to(self.device, torch.float32)
+                _, post, _ = self.AE(x, co, ct)
+                for j, i in enumerate(sel):
+                    out[i] = post[j]
+        return out
+
+    # -- reference-shaped API -----------------------------------------------------------------------
+    def convert(self, source: Utterance, target: SpeakerRef, target_data: object = None, cut: bool = False,
+                n_frames: int = 400, overlap: float = 0.5) -> torch.Tensor:
+        """One conversion (reference `convert`, `:88-211`, mel in / mel out).  With `cut` the utterance is chunked and
+        overlap-averaged through `batch_forward` semantics (`:163-169`), otherwise it is one sequence (`:172-174`).
+        The source embedding is the SOURCE speaker's (the reference hard-codes `speakers['hilde']`, `:147`, with the
+        intended call commented out at `:145`)."""
+        c_s = self.embedding(source.speaker, source.speaker_data)
+        c_t = self.embedding(target, target_data)
+        if not cut:
+            return self.convert_batch([source.mel], [c_s], [c_t])[0]
+        chunks = chunk_mel(source.mel, n_frames, overlap)
+        posts = self.convert_batch(list(chunks), [c_s] * len(chunks), [c_t] * len(chunks))
+        return overlap_average(torch.stack(posts), overlap)
+
+    def match(self, sources: Sequence[Utterance], targets: Sequence[Union[Utterance, Hashable]],
+              match_method: str = "all_combinations") -> List[Tuple[int, int]]:
+        """(source index, target index) pairs in the reference's order (`:383-388`)."""
+        if match_method == "align":
+            if len(sources) != len(targets):
+                raise AssertionError("align needs as many targets as sources")
+            return list(zip(range(len(sources)), range(len(targets))))
+        if match_method == "all_combinations":
+            return list(product(range(len(sources)), range(len(targets))))
+        raise ValueError(f"unknown match_method {match_method!r}")
+
+    def convert_multiple(self, sources: Sequence[Utterance], targets: Sequence[Union[Utterance, Hashable]],
+                         match_method: str = "all_combinations", bidirectional: bool = False,
+                         distributed: bool = False, gather: bool = True) -> List[Optional[torch.Tensor]]:
+        """reference `convert_multiple` (`:346-398`) as batched work: same pairing and output order, but speakers are
+        embedded once each, pairs are bucketed by length, and with `distributed` the pair list is split in contiguous
+        blocks over the ranks (results of other ranks are `None` unless `gather`)."""
+        pairs: List[Tuple[Utterance, SpeakerRef, object]] = []
+        for si, ti in self.match(sources, targets, match_method):
+            tgt = targets[ti]
+            if isinstance(tgt, Utterance):
+                pairs.append((sources[si], tgt.speaker, tgt.speaker_data))
+            else:
+                if bidirectional:
+                    raise AssertionError("Cannot convert in both ways if a mean speaker embedding is to be used")
+                pairs.append((sources[si], tgt, None))
+        if bidirectional:   # targets become sources (`:394-396`)
+            for ti, si in self.match(targets, sources, match_method):
+                pairs.append((targets[ti], sources[si].speaker, sources[si].speaker_data))
+
+        rank, world = 0, 1
+        if distributed:
+            import torch.distributed as dist
+            rank, world = dist.get_rank(), dist.get_world_size()
+        mine = shard_range(len(pairs), rank, world)
+        # one embedding per distinct speaker this rank touches (a 256-float vector; cheaper to recompute than to exchange)
+        mels = [pairs[i][0].mel for i in mine]
+        c_s = [self.embedding(pairs[i][0].speaker, pairs[i][0].speaker_data) for i in mine]
+        c_t = [self.embedding(pairs[i][1], pairs[i][2]) for i in mine]
+        local = self.convert_batch(mels, c_s, c_t)
+        results: List[Optional[torch.Tensor]] = [None] * len(pairs)
+        for i, r in zip(mine, local):
+            results[i] = r
+        if distributed and gather and world > 1:
+            import torch.distributed as dist
+            blocks: List[object] = [None] * world
+            dist.all_gather_object(blocks, [r.cpu() for r in local])     # off the hot path (optional gather)
+            for rk, block in enumerate(blocks):
+                for i, r in zip(shard_range(len(pairs), rk, world), block):
+                    results[i] = r
+        return results
+
+
+class HostPipeline:
+    """Throughput path for host-resident batches: step i+1's host->device copy and step i-1's device->host copy run on
+    a copy stream while step i computes, with double-buffered device inputs/outputs and pinned host outputs.
+    The generator call itself is the unchanged public `AutoEncoder.forward`."""
+
+    def __init__(self, auto_encoder, device: torch.device):
+        self.AE = auto_encoder
+        self.device = torch.device(device)
+        self.copy_stream = torch.cuda.Stream(self.device)
+
+    def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]], outputs: Sequence[Tuple[torch.Tensor, ...]]):
+        """`batches`: pinned host (x, c_org, c_trg); `outputs`: per batch pinned host (mel, mel_post, codes) to fill.
+        Returns after everything is enqueued; the caller synchronises."""
+        compute = torch.cuda.current_stream(self.device)
+        batches = list(batches)
+        n = len(batches)
+        if n == 0:
+            return
+        dev_in = [None, None]
+        in_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        out_done = [torch.cuda.Event(), torch.cuda.Event()]
+        comp_done = [torch.cuda.Event(), torch.cuda.Event()]
+        keep = [None, None]
+
+        def h2d(i):
+            with torch.cuda.stream(self.copy_stream):
+                if i >= 2:
+                    self.copy_stream.wait_event(comp_done[i % 2])     # the slot's previous inputs have been consumed
+                dev_in[i % 2] = tuple(t.to(self.device, non_blocking=True) for t in batches[i])
+                in_ready[i % 2].record(self.copy_stream)
+
+        h2d(0)
+        for i in range(n):
+            if i + 1 < n:
+                h2d(i + 1)
+            compute.wait_event(in_ready[i % 2])
+            res = self.AE(*dev_in[i % 2])
+            for t in dev_in[i % 2]:
+                t.record_stream(compute)
+            comp_done[i % 2].record(compute)
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(comp_done[i % 2])
+                for dst, src in zip(outputs[i], res):
+                    dst.copy_(src, non_blocking=True)
+                out_done[i % 2].record(self.copy_stream)
+            for t in res:
+                t.record_stream(self.copy_stream)
+            keep[i % 2] = res
+        compute.wait_event(out_done[(n - 1) % 2])
+        if n > 1:
+            compute.wait_event(out_done[(n - 2) % 2])
