@@ -28,7 +28,8 @@ class OracleAE:
 def make_world(n_src=3, n_trg=2, lengths=(64, 96, 64)):
     srcs = []
     for i in range(n_src):
-        x, c, _ = synth_inputs(1, lengths[i % len(lengths)], seed=100 + i)
+        x, _, _ = synth_inputs(1, lengths[i % len(lengths)], seed=100 + i)
+        _, c, _ = synth_inputs(1, 32, seed=300 + i % 2)                     # speaker data belongs to the speaker
         srcs.append(Utterance(x[0], f"src{i % 2}", speaker_data=c[0]))      # two source speakers for three utterances
     trgs = []
     for j in range(n_trg):
@@ -57,7 +58,6 @@ def test_convert_multiple_order_dedupe_and_bucketing():
     # one forward per length bucket (64: 4 pairs, 96: 2 pairs), never a padded batch
     assert sorted(ae.calls) == [(2, 80, 96), (4, 80, 64)]
     # reference order: product(sources, targets); each result equals the single-pair conversion
-    # (a speaker's embedding is the one computed the first time the speaker was seen - srcs[2] shares 'src0' with srcs[0])
     k = 0
     for s in srcs:
         for t in trgs:
