@@ -75,6 +75,8 @@ struct avc_ctx {
     // tensor-core plan cache (valid for one (B,T,workspace) triple)
     std::vector<TcGemmPlan*> plans;
     std::vector<TcLstmPlan*> lplans;
+    std::vector<LlLstmPlan*> llplans;
+    bool old_lstm = false;     // AVC_LSTM_IMPL=tc: step-counter + TMA recurrence (tc_lstm.cu) instead of ll_lstm.cu
     bool simt_lstm = false;    // AVC_SIMT_LSTM=1: debugging aid, per-step CUDA-core recurrences in the bf16 mode
     int plan_B = 0, plan_T = 0;
     void* plan_ws = nullptr;
@@ -252,7 +254,7 @@ struct Runner {
     cudaStream_t s;
     int B, T;
     int rc = AVC_OK;
-    size_t plan_cursor = 0, lplan_cursor = 0;
+    size_t plan_cursor = 0, lplan_cursor = 0, llplan_cursor = 0;
     bool building_plans = false;
 
     bool ok() const { return rc == AVC_OK; }
@@ -309,6 +311,19 @@ struct Runner {
         const Layer& L = h->layers[lid_hh];
         mark(lid_hh <= L_ENC_L1_HH ? AVC_PHASE_ENC_LSTM : (lid_hh == L_DEC_LSTM1_HH ? AVC_PHASE_LSTM1 : AVC_PHASE_LSTM2));
         const size_t hs = dtype_size(h_type);
+        if (use_tc() && !h->simt_lstm && !h->old_lstm && ndir == 1 && h_type == DT_BF16 && L.w_type == DT_BF16 && H % 256 == 0) {
+            // persistent tensor-core recurrence, in-band validity exchange (ll_lstm.cu)
+            if (building_plans) {
+                const char* why = nullptr;
+                LlLstmPlan* plan = ll_lstm_plan_create(L.w_dev, Gx, Tg, gx_div, Y, wsp->Yb, B, T, H, h->num_sms, &why);
+                if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core LSTM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
+                h->llplans.push_back(plan);
+            }
+            int n = 0;
+            check(launch_ll_lstm(h->llplans[llplan_cursor++], s, &n), L.name.c_str());
+            h->launches += n;
+            return;
+        }
         if (use_tc() && !h->simt_lstm && ndir == 1 && h_type == DT_BF16 && L.w_type == DT_BF16 && H % 64 == 0) {
             // persistent tensor-core recurrence (tc_lstm.cu)
             if (building_plans) {
@@ -373,6 +388,8 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
             h->plans.clear();
             for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
             h->lplans.clear();
+            for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
+            h->llplans.clear();
             r.building_plans = true;
             h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_encode_only = encode_only;
         }
@@ -435,6 +452,8 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         h->plans.clear();
         for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
         h->lplans.clear();
+        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
+        h->llplans.clear();
         h->plan_ws = nullptr;
     }
     return r.rc;
@@ -466,6 +485,8 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
     h->force_simt = fs && fs[0] == '1';
     const char* sl = getenv("AVC_SIMT_LSTM");
     h->simt_lstm = sl && sl[0] == '1';
+    const char* li = getenv("AVC_LSTM_IMPL");
+    h->old_lstm = li && li[0] == 't';
     for (int i = 0; i < L_COUNT; ++i) h->layers[i].name = kLayerNames[i];
     if (device >= 0) {
         cudaError_t e = cudaSetDevice(device);
@@ -477,6 +498,7 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
         if (precision == AVC_PREC_BF16 && !h->force_simt) {
             const char* why = tc_init();
             if (!why) why = tc_lstm_init();
+            if (!why) why = ll_lstm_init();
             if (why) { int rc = fail(nullptr, AVC_ERR_CUDA, "tensor-core kernel setup: %s", why); delete h; return rc; }
         }
     }
@@ -530,6 +552,8 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
         h->plans.clear();
         for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
         h->lplans.clear();
+        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
+        h->llplans.clear();
         h->plan_ws = nullptr;
     }
     h->loaded = true;
@@ -627,6 +651,7 @@ void avc_destroy(avc_handle h) {
         }
         for (auto* p : h->plans) tc_gemm_plan_destroy(p);
         for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
+        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
         for (auto ev : h->prof_events) cudaEventDestroy(ev);
     }
     delete h;

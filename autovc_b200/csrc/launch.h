@@ -32,6 +32,15 @@ void tc_lstm_plan_destroy(TcLstmPlan* plan);
 int tc_lstm_ready_words(int B, int T);
 cudaError_t launch_tc_lstm(const TcLstmPlan* plan, cudaStream_t s, int* launches);
 
+// ll_lstm.cu (persistent weight-stationary LSTM recurrence, tcgen05; h exchanged through L2 with in-band validity)
+struct LlLstmPlan;
+const char* ll_lstm_init();
+size_t ll_lstm_exchange_bytes(int B, int T, int H);
+LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, void* Yx, int B, int T, int H,
+                                int num_sms, const char** err);
+void ll_lstm_plan_destroy(LlLstmPlan* plan);
+cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches);
+
 // enc_lstm.cu (encoder BiLSTM, H=32: one warp per 16 utterances x direction, W_hh in registers, mma.sync)
 bool enc_lstm_supported(int dim_neck);
 cudaError_t launch_enc_lstm_l0(const float* Gx, const void* Whh_bf16, void* Y_bf16, int B, int T, cudaStream_t s);

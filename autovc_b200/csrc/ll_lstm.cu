@@ -1,0 +1,521 @@
+// Persistent weight-stationary LSTM recurrence on the tensor cores (sm_100a).  Used for the decoder's lstm1 (H=512)
+// and lstm2 (H=1024, two layers run one after the other)  [reference decoder.py:37,53,65,74].
+//
+// Decomposition: grid = (H/32 unit slices) x (batch tiles of 64 utterances), all CTAs co-resident (cooperative
+// launch, one CTA per SM; lstm2 at B=256: 32 x 4 = 128 CTAs).  The GEMM of a step is computed TRANSPOSED:
+//   D[128 gate rows x 64 utterances] (TMEM, fp32) = W_slice[128 x H] . h_{t-1}^T[H x 64]
+// so that the resident operand is A and the streamed operand is B:
+//   * A = the CTA's 128 gate rows (32 hidden units x i,f,g,o, unit-major packing) of W_hh.  They live in TENSOR
+//     MEMORY for the whole sequence (448 of the 512 columns = K 0..895; the rest of K, if any, in shared memory),
+//     so an MMA reads only the 2 KiB h block from shared memory and runs at the tensor-pipe floor.
+//   * B = h_{t-1} of the CTA's 64 utterances, [64 x H] bf16 = 128 KiB per step at H=1024 - half of what a
+//     128-utterance x 16-unit tiling must ingest per SM and per step.  The measured bound of this kernel family is
+//     the L2 -> SM path (latency 1.2-2k cycles, ~4 KB/clk over the whole chip; profiles/r1_lstm_step_timeline.md),
+//     so bytes per SM and round trips per step are what the design minimises.
+//
+// Exchange protocol ("the data is the flag"): CTAs exchange h through an L2-resident buffer Yx laid out as
+// [T][batch tile][H/8 planes][64 rows][8 bf16], pre-filled with the bit pattern 0xFFFF (a NaN that the float->bf16
+// conversion never produces: it canonicalises NaN to 0x7FFF).  Producers simply store their 16-byte pieces of h_t;
+// consumers read with strong (L1-bypassing) coalesced 16-byte loads and treat any 32-bit word of all ones as "not
+// written yet" (32-bit accesses are single-copy atomic) and poll it again.  No step counter, no release/acquire fence
+// pair, no second round trip between "flag seen" and "data fetched".  All of a step's loads of a warp are in flight
+// together (one wave), and a warp owns one K chunk (two producer CTAs), so chunks are consumed as their producers
+// finish and the skew between CTAs overlaps with the stream.
+//
+// Warp roles (512 threads; 128 registers per thread):
+//   warps 0-15  loaders : one K chunk (or part of one) each: poll a 16-byte canary per lane, then fetch the chunk's
+//                         pieces, validate, store them as a 128B-swizzled K-major operand tile (generic-proxy stores +
+//                         fence.proxy.async) and arrive on the chunk's mbarrier
+//   warps 0-7   epilogue: tcgen05.ld the gate pre-activations (lane = gate row, 32 utterance columns per thread), add the
+//                         hoisted input projection Gx_t (staged in shared memory with cp.async), activation, 4x4 quad
+//                         transpose with shuffles (lane j ends with i,f,g,o of 8 utterances), cell update (c in registers),
+//                         h_t -> shared-memory transpose -> 16-byte stores to Yx (exchange) and Y (next layer)
+//   MMA issue           : by warp 15 after its own chunk, whole-warp with uniform operands (one elected lane), chunks in a
+//                         fixed order (bitwise reproducible accumulation), gated by one mbarrier per group of four loader warps
+// The input projection x_t W_ih^T + b_ih + b_hh for all t is hoisted into one dense GEMM (tc_gemm.cu) beforehand.
+//
+// Every spin/wait is bounded: a protocol bug traps (CUDA error) instead of hanging the GPU.
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include <cuda.h>
+
+#include "common.cuh"
+#include "launch.h"
+#include "ptx.cuh"
+
+namespace avc {
+
+namespace {
+
+constexpr int SLICE_UNITS = 32;           // hidden units per CTA
+constexpr int MROWS = 4 * SLICE_UNITS;    // gate rows per CTA = UMMA M = TMEM lanes
+constexpr int TILE_N = 64;                // utterances per CTA = UMMA N
+constexpr int KBLK = 64;                  // K elements per chunk (128 bytes per operand row)
+constexpr int W_BLK_BYTES = MROWS * KBLK * 2;     // 16 KiB (shared-memory part of W)
+constexpr int H_BLK_BYTES = TILE_N * KBLK * 2;    // 8 KiB
+constexpr int PLANE_ELEMS = 8;            // Yx plane width: 8 bf16 = 16 B
+constexpr int PLANE_STRIDE = TILE_N * PLANE_ELEMS;      // elements between planes
+constexpr int LOAD_WARPS = 16, EPI_WARPS = 8;
+constexpr int MMA_WARP = LOAD_WARPS - 1;  // the last loader warp also issues the MMAs
+constexpr int NUM_THREADS = LOAD_WARPS * 32;            // 512: four warps per scheduler, 128 registers per thread
+constexpr int EPI_THREADS = EPI_WARPS * 32;             // 256
+constexpr int GX_BYTES = TILE_N * MROWS * 4;            // 32 KiB: Gx_t of the tile, [utterance][gate row] fp32
+constexpr int HT_BYTES = TILE_N * SLICE_UNITS * 2;      // 4 KiB: h_t transpose staging, [utterance][unit] bf16
+constexpr uint32_t D_COLS = TILE_N;       // one accumulator
+constexpr uint32_t W_COL0 = D_COLS;       // W chunks follow: 32 columns each
+constexpr int MAX_TMEM_CHUNKS = (512 - (int)D_COLS) / 32;   // 14
+constexpr uint32_t TMEM_COLS = 512;
+constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
+constexpr int MAX_KB = 16;
+
+struct LlLstmArgs {
+    int B, T, H;
+    int gx_div;                  // Gx row for frame t is t / gx_div (lstm1 reads the de-duplicated projection)
+    const float* Gx;             // [B][Tg][4H] fp32, unit-major gate order, bias included
+    const __nv_bfloat16* Whh;    // [4H][H] bf16, unit-major gate rows
+    __nv_bfloat16* Y;            // [B][T][H] bf16 output sequence for the next layer
+    __nv_bfloat16* Yx;           // exchange copy: [T][tiles][H/8][64][8] bf16, pre-filled with 0xFF
+    int tiles, tile0;            // batch tiles in Yx, first tile of this launch
+    long long y_sb, y_st;        // element strides of Y along utterance / frame
+    long long gx_sb, gx_st;      // same for Gx rows (frame index t / gx_div)
+    uint32_t idesc;
+    long long* trace;            // optional clock64 trace of CTA (0,0) (AVC_LSTM_TRACE=1), nullptr normally
+};
+
+constexpr int TRACE_T0 = 8, TRACE_STEPS = 8, TRACE_PTS = 32;   // 0..5 phase stamps, 8+kc: chunk kc seen by the MMA thread
+#define AVC_TRACE(pt) do { if (a.trace && blockIdx.x == 0 && blockIdx.y == 0 && t >= TRACE_T0 && t < TRACE_T0 + TRACE_STEPS) \
+    a.trace[(t - TRACE_T0) * TRACE_PTS + (pt)] = clock64(); } while (0)
+
+__device__ __forceinline__ uint4 ld_strong(const void* p) {
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_strong(void* p, uint4 v) {
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ bool unwritten(const uint4& v) {
+    return v.x == SENTINEL || v.y == SENTINEL || v.z == SENTINEL || v.w == SENTINEL;
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_shared_u16(uint32_t addr, uint16_t v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
+
+template <int NKB>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
+    constexpr int NKB_T = NKB < MAX_TMEM_CHUNKS ? NKB : MAX_TMEM_CHUNKS;   // W chunks resident in tensor memory
+    constexpr int NKB_S = NKB - NKB_T;                                     // W chunks resident in shared memory
+    constexpr int WPC = LOAD_WARPS / NKB;                                  // loader warps per chunk: 1, 2 or 4
+    static_assert(NKB == 16 || NKB == 8 || NKB == 4, "H must be 1024, 512 or 256");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sW = smem;                                        // NKB_S x 16 KiB: W columns beyond the TMEM-resident part
+    uint8_t* sH = sW + NKB_S * W_BLK_BYTES;                    // NKB x 8 KiB: h_{t-1} operand tiles
+    uint8_t* sGx = sH + NKB * H_BLK_BYTES;                     // 32 KiB
+    uint8_t* sHT = sGx + GX_BYTES;                             // 4 KiB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sHT + HT_BYTES);
+    uint64_t* wfull = bars;
+    uint64_t* gfull = bars + 4;                                // [4] the chunks of loader-warp group g (warps 4g..4g+3) are in shared memory
+    uint64_t* acc_full = wfull + 1;                            // the MMAs of a step are complete
+    uint64_t* acc_empty = wfull + 2;                           // the epilogue has read the accumulator
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull + 3);
+
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp: provably uniform
+    const int ns = blockIdx.x;            // unit slice (32 units)
+    const int bt = blockIdx.y;            // batch tile (64 utterances)
+    const int b0 = bt * TILE_N;
+    const size_t tile_elems = (size_t)a.H * TILE_N;                         // one (t, tile) block of Yx
+    const size_t step_elems = tile_elems * a.tiles;
+    __nv_bfloat16* yx_tile = a.Yx + (size_t)(a.tile0 + bt) * tile_elems;    // + t * step_elems
+
+    if (warp == 0) {
+        if (lane == 0) {
+            if (NKB_S > 0) ptx::prefetch_tmap(&tmW);
+            ptx::mbar_init(wfull, 1);
+            for (int g = 0; g < 4; ++g) ptx::mbar_init(&gfull[g], 4);
+            ptx::mbar_init(acc_full, 1);
+            ptx::mbar_init(acc_empty, EPI_WARPS);
+            ptx::fence_barrier_init();
+        }
+        __syncwarp();
+        ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    // the CTA owns the SM and allocates all 512 columns, so the allocation starts at column 0 / lane 0: treating the base as
+    // the constant 0 lets the compiler keep every TMEM address and descriptor of the MMA loop in uniform registers
+    if (*tmem_slot != 0u) { if (threadIdx.x == 0) printf("autovc_b200: unexpected TMEM base %u\n", *tmem_slot); __trap(); }
+    constexpr uint32_t tmem_base = 0u;
+
+    // ---- resident W: chunks 0..NKB_T-1 -> tensor memory (lane = gate row, 32 columns per chunk), the rest -> smem ----
+    if (warp < 4) {
+        const int R = warp * 32 + lane;
+        const __nv_bfloat16* wrow = a.Whh + (size_t)(ns * MROWS + R) * a.H;
+        const uint32_t wl = tmem_base + W_COL0 + ((uint32_t)(warp * 32) << 16);
+        for (int kc = 0; kc < NKB_T; ++kc) {
+            uint4 v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __ldg(reinterpret_cast<const uint4*>(wrow + kc * KBLK) + i);
+            ptx::tmem_st32(wl + (uint32_t)(kc * 32), reinterpret_cast<const uint32_t(&)[32]>(v));
+        }
+        ptx::tmem_st_wait();
+    }
+    if (NKB_S > 0 && warp == 4 && lane == 0) {
+        ptx::mbar_expect_tx(wfull, (uint32_t)(NKB_S * W_BLK_BYTES));
+        for (int i = 0; i < NKB_S; ++i)
+            ptx::tma_load_2d(sW + i * W_BLK_BYTES, &tmW, wfull, (NKB_T + i) * KBLK, ns * MROWS);
+        ptx::mbar_wait(wfull, 0);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+
+    {
+        // ===================== loaders (warps 0..15) + epilogue (warps 0..7) =====================
+        const bool epi = warp < EPI_WARPS;
+        // ---- loader geometry: this warp's chunk and, per piece i, the (row, plane) of the lane ----
+        const int kc = warp / WPC, sub = warp % WPC;
+        auto piece_row = [&](int i) { return WPC == 1 ? (i & 1) * 32 + lane : (WPC == 2 ? sub * 32 + lane : sub * 16 + (lane & 15)); };
+        auto piece_plane = [&](int i) { return WPC == 1 ? (i >> 1) : (WPC == 2 ? i : 2 * i + (lane >> 4)); };
+        const uint32_t sH_chunk = ptx::smem_u32(sH) + (uint32_t)(kc * H_BLK_BYTES);
+        const __nv_bfloat16* chunk_base = yx_tile + (size_t)kc * 8 * PLANE_STRIDE;
+
+        // ---- epilogue geometry ----
+        const int q = warp & 3, half = (warp >> 2) & 1;       // TMEM lane quarter; utterance half (32 columns)
+        const int R = q * 32 + lane;                          // gate row of this CTA = TMEM lane
+        const int gj = lane & 3;                              // gate of this lane: 0=i 1=f 2=g 3=o
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 32);
+        const float act_s = gj == 2 ? 2.0f : 1.0f, act_o = gj == 2 ? -1.0f : 0.0f;   // tanh(x) = 2 sigmoid(2x) - 1
+        float c[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) c[k] = 0.0f;
+        const uint32_t gx_smem = ptx::smem_u32(sGx);
+        const uint32_t ht_smem = ptx::smem_u32(sHT);
+        // Gx staging: thread e copies pieces e + 256 i (i < 8): utterance = id / 32, 16-byte segment = id % 32
+        auto stage_gx = [&](int t) {
+            const size_t toff = (size_t)(t / a.gx_div) * a.gx_st + (size_t)ns * MROWS;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int id = threadIdx.x + EPI_THREADS * i;
+                const int u = id >> 5, seg = id & 31;
+                const int b = b0 + u < a.B ? b0 + u : a.B - 1;
+                cp_async16(gx_smem + (uint32_t)(u * (MROWS * 4) + seg * 16), a.Gx + (size_t)b * a.gx_sb + toff + seg * 4);
+            }
+            cp_async_commit();
+        };
+        // output geometry of the final 16-byte stores: thread e -> utterance e/4, 8-unit piece e%4
+        const int ou = threadIdx.x >> 2, op = threadIdx.x & 3;
+        const bool ovalid = b0 + ou < a.B;
+        __nv_bfloat16* y_out = a.Y + (size_t)(ovalid ? b0 + ou : 0) * a.y_sb + (size_t)ns * SLICE_UNITS + op * 8;
+        __nv_bfloat16* yx_out = yx_tile + ((size_t)(ns * 4 + op) * TILE_N + (ou & (TILE_N - 1))) * PLANE_ELEMS;
+        if (epi) stage_gx(0);
+
+        for (int t = 0; t < a.T; ++t) {
+            if (t >= 1) {
+                // ---- h_{t-1} chunk: L2 -> registers (poll) -> swizzled operand tile in shared memory ----
+                const __nv_bfloat16* src = chunk_base + (size_t)(t - 1) * step_elems;
+                {   // step start: poll one 16-byte canary per lane; whole-chunk polls would compete with the producers' stores
+                    const __nv_bfloat16* p = src + (size_t)piece_plane(0) * PLANE_STRIDE + piece_row(0) * PLANE_ELEMS;
+                    uint4 cn = ld_strong(p);
+                    for (uint32_t spin = 0; unwritten(cn); ++spin) {
+                        cn = ld_strong(p);
+                        if (spin > (1u << 22)) { printf("autovc_b200: lstm h canary timed out (slice %d tile %d t %d warp %d)\n", ns, bt, t, warp); __trap(); }
+                    }
+                }
+                if (threadIdx.x == 0) AVC_TRACE(0);
+                uint4 v[NKB];
+#pragma unroll
+                for (int i = 0; i < NKB; ++i)
+                    v[i] = ld_strong(src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS);
+                // the MMAs of step t-1 still read the tiles until acc_full(t-1): normally long past
+                if (t >= 2 && !epi) ptx::mbar_wait(acc_full, (uint32_t)(t - 2) & 1);
+#pragma unroll
+                for (int i = 0; i < NKB; ++i) {
+                    const __nv_bfloat16* p = src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS;
+                    uint32_t spin = 0;
+                    while (unwritten(v[i])) {               // not written yet: poll again
+                        v[i] = ld_strong(p);
+                        if (++spin > (1u << 22)) {
+                            printf("autovc_b200: lstm h poll timed out (slice %d tile %d t %d chunk %d piece %d lane %d)\n", ns, bt, t, kc, i, lane);
+                            __trap();
+                        }
+                    }
+                    const int row = piece_row(i), pl = piece_plane(i);
+                    st_shared_v4(sH_chunk + (uint32_t)(row * 128 + ((pl ^ (row & 7)) << 4)), v[i]);
+                }
+                ptx::fence_proxy_async_smem();          // generic-proxy smem writes -> tcgen05.mma (async proxy) reads
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&gfull[warp >> 2]);
+                if (warp == MMA_WARP) {
+                    // the last loader warp issues the MMAs of the step, chunk by chunk in a fixed order (the accumulation
+                    // order must not depend on timing: results are bitwise reproducible).  Whole-warp, uniform operands.
+                    if (t >= 2) ptx::mbar_wait(acc_empty, (uint32_t)(t - 2) & 1);   // epilogue of step t-1 has read D
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        ptx::mbar_wait(&gfull[g], (uint32_t)(t - 1) & 1);
+                        ptx::tc_fence_after();
+                        if (g == 0) AVC_TRACE(2);
+#pragma unroll
+                        for (int cc = 0; cc < NKB / 4; ++cc) {
+                            const int c = g * (NKB / 4) + cc;
+                            const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sH) + (uint32_t)(c * H_BLK_BYTES));
+                            if (c < NKB_T) {
+                                const uint32_t a_tmem = tmem_base + W_COL0 + (uint32_t)(c * 32);
+#pragma unroll
+                                for (int k = 0; k < KBLK / 16; ++k)
+                                    ptx::umma_f16_ts_warp(tmem_base, a_tmem + (uint32_t)(k * 8), bdesc + (uint64_t)(k * 2), a.idesc, (c | k) != 0 ? 1u : 0u);
+                            } else {
+                                const uint64_t adesc = ptx::umma_desc_sw128(ptx::smem_u32(sW + (c - NKB_T) * W_BLK_BYTES));
+#pragma unroll
+                                for (int k = 0; k < KBLK / 16; ++k)
+                                    ptx::umma_f16_warp(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, (c | k) != 0 ? 1u : 0u);
+                            }
+                        }
+                    }
+                    ptx::umma_commit_warp(acc_full);
+                    AVC_TRACE(3);
+                }
+                if (threadIdx.x == 0) AVC_TRACE(1);
+            }
+            if (!epi) continue;
+
+            // ---- epilogue: gates, cell state, h_t ----
+            cp_async_wait_all();                       // own pieces of Gx_t ...
+            named_bar_sync(2, EPI_THREADS);            // ... and everybody else's
+            float act[32];
+            if (t >= 1) {
+                ptx::mbar_wait(acc_full, (uint32_t)(t - 1) & 1);
+                if (threadIdx.x == 0) AVC_TRACE(4);
+                ptx::tc_fence_after();
+                uint32_t acc[2][16];
+                ptx::tmem_ld16(taddr, acc[0]);
+                ptx::tmem_ld16(taddr + 16, acc[1]);
+                ptx::tmem_ld_wait();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(acc_empty);
+#pragma unroll
+                for (int k = 0; k < 32; ++k) act[k] = __uint_as_float(acc[k >> 4][k & 15]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 32; ++k) act[k] = 0.0f;
+            }
+            // + Gx_t[utterance half*32 + k][gate row R], then this lane's activation
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+                const float x = act[k] + ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
+                act[k] = __fdividef(act_s, 1.0f + __expf(-act_s * x)) + act_o;
+            }
+            // 4x4 quad transpose (blocks of 8 columns): lane j ends with all four gates of columns 8j..8j+7
+            float X[16], Y2[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const float send = (gj & 2) ? act[k] : act[16 + k];
+                X[k] = (gj & 2) ? act[16 + k] : act[k];                      // own gate gj
+                Y2[k] = __shfl_xor_sync(0xffffffffu, send, 2);               // gate gj ^ 2
+            }
+            uint32_t hp[4];
+#pragma unroll
+            for (int k = 0; k < 8; k += 2) {
+                float hv[2];
+#pragma unroll
+                for (int w = 0; w < 2; ++w) {
+                    const int kk = k + w;
+                    const float sx = (gj & 1) ? X[kk] : X[8 + kk], sy = (gj & 1) ? Y2[kk] : Y2[8 + kk];
+                    const float kx = (gj & 1) ? X[8 + kk] : X[kk], ky = (gj & 1) ? Y2[8 + kk] : Y2[kk];
+                    const float rx = __shfl_xor_sync(0xffffffffu, sx, 1), ry = __shfl_xor_sync(0xffffffffu, sy, 1);
+                    // kx: gate gj, ky: gj^2, rx: gj^1, ry: gj^3
+                    const float e0 = (gj & 1) ? rx : kx, e2 = (gj & 1) ? ry : ky;     // gates (gj & 2) and (gj & 2) ^ 2
+                    const float e1 = (gj & 1) ? kx : rx, e3 = (gj & 1) ? ky : ry;     // gates (gj & 2) + 1 and its ^ 2
+                    const float ig = (gj & 2) ? e2 : e0, gg = (gj & 2) ? e0 : e2;
+                    const float fg = (gj & 2) ? e3 : e1, og = (gj & 2) ? e1 : e3;
+                    c[kk] = fg * c[kk] + ig * gg;
+                    hv[w] = og * (1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * c[kk])));
+                }
+                __nv_bfloat162 h2 = __floats2bfloat162_rn(hv[0], hv[1]);
+                hp[k >> 1] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            // transpose through shared memory: hT[utterance][unit], 16-byte pieces XOR-swizzled by (utterance / 8) & 3
+            {
+                const int unit = q * 8 + (lane >> 2);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int u = half * 32 + gj * 8 + k;
+                    const int piece = (unit >> 3) ^ ((u >> 3) & 3);
+                    const uint16_t hv16 = (uint16_t)((k & 1) ? (hp[k >> 1] >> 16) : (hp[k >> 1] & 0xffffu));
+                    st_shared_u16(ht_smem + (uint32_t)(u * 64 + piece * 16 + (unit & 7) * 2), hv16);
+                }
+            }
+            named_bar_sync(1, EPI_THREADS);
+            {
+                const uint4 hv4 = ld_shared_v4(ht_smem + (uint32_t)(ou * 64 + ((op ^ ((ou >> 3) & 3)) << 4)));
+                // utterances beyond B hold bounded garbage: they are exchanged like any other row, so loaders need no
+                // row masks, and they are never written to Y
+                if (t + 1 < a.T) st_strong(yx_out + (size_t)t * step_elems, hv4);
+                if (ovalid) *reinterpret_cast<uint4*>(y_out + (size_t)t * a.y_st) = hv4;
+            }
+            if (threadIdx.x == 0) AVC_TRACE(5);
+            if (t + 1 < a.T) stage_gx(t + 1);
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode_ll = nullptr;
+
+const void* kernel_for(int nkb) {
+    switch (nkb) {
+        case 16: return (const void*)ll_lstm_kernel<16>;
+        case 8: return (const void*)ll_lstm_kernel<8>;
+        default: return (const void*)ll_lstm_kernel<4>;
+    }
+}
+
+int smem_for(int nkb) {
+    const int nkb_s = nkb > MAX_TMEM_CHUNKS ? nkb - MAX_TMEM_CHUNKS : 0;
+    return nkb_s * W_BLK_BYTES + nkb * H_BLK_BYTES + GX_BYTES + HT_BYTES + 1024 + 512;
+}
+
+}  // namespace
+
+struct LlLstmPlan {
+    CUtensorMap tmW;
+    std::vector<LlLstmArgs> args;
+    std::vector<dim3> grids;
+    int nkb;
+    int smem_bytes;
+    void* yx_base; size_t yx_bytes;       // region to pre-fill with the "unwritten" pattern before every launch
+};
+
+const char* ll_lstm_init() {
+    if (g_encode_ll) return nullptr;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return "cuTensorMapEncodeTiled not available from the driver";
+    for (int nkb : {16, 8, 4})
+        if (cudaFuncSetAttribute(kernel_for(nkb), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_for(nkb)) != cudaSuccess)
+            return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed for ll_lstm_kernel";
+    g_encode_ll = reinterpret_cast<EncodeTiledFn>(fn);
+    return nullptr;
+}
+
+size_t ll_lstm_exchange_bytes(int B, int T, int H) { return (size_t)T * ceil_div(B, TILE_N) * TILE_N * H * 2; }
+
+LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, void* Yx, int B, int T, int H,
+                                int num_sms, const char** err) {
+    static thread_local char msg[256];
+    auto bad = [&](const char* m) -> LlLstmPlan* { if (err) *err = m; return nullptr; };
+    if (!g_encode_ll) return bad("ll_lstm_init() not called");
+    if (H != 1024 && H != 512 && H != 256) return bad("hidden size must be 256, 512 or 1024");
+    const int G_n = H / SLICE_UNITS, nkb = H / KBLK;
+    if (G_n > num_sms) return bad("hidden size too large for one co-resident grid");
+    LlLstmPlan* plan = new LlLstmPlan();
+    plan->nkb = nkb;
+    plan->smem_bytes = smem_for(nkb);
+    plan->yx_base = Yx; plan->yx_bytes = ll_lstm_exchange_bytes(B, T, H);
+    {
+        cuuint64_t gdim[2] = {(cuuint64_t)H, (cuuint64_t)4 * H};
+        cuuint64_t gstr[1] = {(cuuint64_t)H * 2};
+        cuuint32_t box[2] = {(cuuint32_t)KBLK, (cuuint32_t)MROWS};
+        cuuint32_t est[2] = {1, 1};
+        CUresult r = g_encode_ll(&plan->tmW, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(Whh_bf16), gdim, gstr, box, est,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(Whh) failed: %d", (int)r); return bad(msg); }
+    }
+    const int tiles_per_launch = num_sms / G_n;
+    const int rows_per_launch = tiles_per_launch * TILE_N;
+    for (int bs = 0; bs < B; bs += rows_per_launch) {
+        const int Bc = (B - bs) < rows_per_launch ? (B - bs) : rows_per_launch;
+        LlLstmArgs a{};
+        a.B = Bc; a.T = T; a.H = H; a.gx_div = gx_div;
+        a.y_sb = (long long)T * H; a.y_st = H; a.gx_sb = (long long)Tg * 4 * H; a.gx_st = 4LL * H;
+        a.Gx = Gx + (size_t)bs * a.gx_sb;
+        a.Whh = reinterpret_cast<const __nv_bfloat16*>(Whh_bf16);
+        a.Y = reinterpret_cast<__nv_bfloat16*>(Y) + (size_t)bs * a.y_sb;
+        a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
+        a.tiles = ceil_div(B, TILE_N); a.tile0 = bs / TILE_N;
+        a.idesc = ptx::umma_idesc_f16(1, MROWS, TILE_N);
+        plan->args.push_back(a);
+        plan->grids.push_back(dim3(G_n, ceil_div(Bc, TILE_N)));
+    }
+    return plan;
+}
+
+void ll_lstm_plan_destroy(LlLstmPlan* plan) { delete plan; }
+
+cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches) {
+    static long long* d_trace = nullptr;
+    const bool tracing = getenv("AVC_LSTM_TRACE") != nullptr;
+    if (tracing && !d_trace) cudaMalloc(&d_trace, sizeof(long long) * (TRACE_STEPS + 1) * TRACE_PTS);
+    // "unwritten" pattern: every 16-bit element = 0xFFFF
+    cudaError_t e = cudaMemsetAsync(plan->yx_base, 0xFF, plan->yx_bytes, s);
+    if (e != cudaSuccess) return e;
+    for (size_t i = 0; i < plan->args.size(); ++i) {
+        LlLstmArgs args = plan->args[i];
+        args.trace = tracing ? d_trace : nullptr;
+        if (tracing) cudaMemsetAsync(d_trace, 0, sizeof(long long) * (TRACE_STEPS + 1) * TRACE_PTS, s);
+        void* kargs[2] = {(void*)&plan->tmW, (void*)&args};
+        // cooperative launch: CTAs wait on one another's output, so co-residency must be guaranteed
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = plan->grids[i]; cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = (size_t)plan->smem_bytes; cfg.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb), kargs);
+        if (e != cudaSuccess) return e;
+        if (launches) ++*launches;
+        if (tracing) {   // debugging aid: synchronous dump of the per-step timeline of CTA (0,0)
+            long long hbuf[(TRACE_STEPS + 1) * TRACE_PTS];
+            cudaStreamSynchronize(s);
+            cudaMemcpy(hbuf, d_trace, sizeof hbuf, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "ll_lstm trace H=%d B=%d grid=(%d,%d): cycles since warp 0 saw its canary: "
+                    "warp0_done warp0_mma_issue warp0_mma_issued acc_seen h_stored | step period\n",
+                    args.H, args.B, plan->grids[i].x, plan->grids[i].y);
+            for (int st = 0; st < TRACE_STEPS; ++st) {
+                const long long* r = hbuf + st * TRACE_PTS;
+                if (!r[0]) continue;
+                fprintf(stderr, "  t=%d:", TRACE_T0 + st);
+                for (int p = 1; p <= 5; ++p) fprintf(stderr, " %6lld", r[p] - r[0]);
+                if (st + 1 < TRACE_STEPS && r[TRACE_PTS]) fprintf(stderr, " | %6lld", r[TRACE_PTS] - r[0]);
+                fprintf(stderr, "\n");
+            }
+        }
+    }
+    return cudaSuccess;
+}
+
+}  // namespace avc
