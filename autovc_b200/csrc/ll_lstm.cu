@@ -50,21 +50,22 @@ namespace {
 
 constexpr int SLICE_UNITS = 32;           // hidden units per CTA
 constexpr int MROWS = 4 * SLICE_UNITS;    // gate rows per CTA = UMMA M = TMEM lanes
-constexpr int TILE_N = 64;                // utterances per CTA = UMMA N
+constexpr int TILE_N = 64;                // utterances per CTA PAIR = UMMA N (each CTA stages half of the rows)
+constexpr int ROWS_CTA = TILE_N / 2;      // utterance rows of h staged by one CTA
 constexpr int KBLK = 64;                  // K elements per chunk (128 bytes per operand row)
 constexpr int W_BLK_BYTES = MROWS * KBLK * 2;     // 16 KiB (shared-memory part of W)
-constexpr int H_BLK_BYTES = TILE_N * KBLK * 2;    // 8 KiB
+constexpr int H_BLK_BYTES = ROWS_CTA * KBLK * 2;  // 4 KiB per CTA and chunk
 constexpr int PLANE_ELEMS = 8;            // Yx plane width: 8 bf16 = 16 B
 constexpr int PLANE_STRIDE = TILE_N * PLANE_ELEMS;      // elements between planes
 constexpr int LOAD_WARPS = 16, EPI_WARPS = 8;
-constexpr int MMA_WARP = LOAD_WARPS - 1;  // the last loader warp also issues the MMAs
+constexpr int MMA_WARP0 = LOAD_WARPS - 2;  // the last two loader warps of the LEADER CTA also issue the MMAs (one K half each)
 constexpr int NUM_THREADS = LOAD_WARPS * 32;            // 512: four warps per scheduler, 128 registers per thread
 constexpr int EPI_THREADS = EPI_WARPS * 32;             // 256
 constexpr int GX_BYTES = TILE_N * MROWS * 4;            // 32 KiB: Gx_t of the tile, [utterance][gate row] fp32
 constexpr int HT_BYTES = TILE_N * SLICE_UNITS * 2;      // 4 KiB: h_t transpose staging, [utterance][unit] bf16
-constexpr uint32_t D_COLS = TILE_N;       // one accumulator
+constexpr uint32_t D_COLS = 2 * TILE_N;   // two accumulators (one per issuing warp: K halves), summed in a fixed order
 constexpr uint32_t W_COL0 = D_COLS;       // W chunks follow: 32 columns each
-constexpr int MAX_TMEM_CHUNKS = (512 - (int)D_COLS) / 32;   // 14
+constexpr int MAX_TMEM_CHUNKS = (512 - (int)D_COLS) / 32;   // 12
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
 constexpr int MAX_KB = 16;
@@ -132,7 +133,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sW = smem;                                        // NKB_S x 16 KiB: W columns beyond the TMEM-resident part
-    uint8_t* sH = sW + NKB_S * W_BLK_BYTES;                    // NKB x 8 KiB: h_{t-1} operand tiles
+    uint8_t* sH = sW + NKB_S * W_BLK_BYTES;                    // NKB x 4 KiB: this CTA's 32 rows of the h_{t-1} operand tiles
     uint8_t* sGx = sH + NKB * H_BLK_BYTES;                     // 32 KiB
     uint8_t* sHT = sGx + GX_BYTES;                             // 4 KiB
     uint64_t* bars = reinterpret_cast<uint64_t*>(sHT + HT_BYTES);
@@ -146,6 +147,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     const int ns = blockIdx.x;            // unit slice (32 units)
     const int bt = blockIdx.y;            // batch tile (64 utterances)
     const int b0 = bt * TILE_N;
+    const uint32_t crank = ptx::cluster_ctarank();   // 0 = leader of the CTA pair (adjacent unit slices, same batch tile)
     const size_t tile_elems = (size_t)a.H * TILE_N;                         // one (t, tile) block of Yx
     const size_t step_elems = tile_elems * a.tiles;
     __nv_bfloat16* yx_tile = a.Yx + (size_t)(a.tile0 + bt) * tile_elems;    // + t * step_elems
@@ -154,16 +156,17 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         if (lane == 0) {
             if (NKB_S > 0) ptx::prefetch_tmap(&tmW);
             ptx::mbar_init(wfull, 1);
-            for (int g = 0; g < 4; ++g) ptx::mbar_init(&gfull[g], 4);
-            ptx::mbar_init(acc_full, 1);
-            ptx::mbar_init(acc_empty, EPI_WARPS);
+            for (int g = 0; g < 4; ++g) ptx::mbar_init(&gfull[g], 8);     // 4 loader warps of each CTA of the pair
+            ptx::mbar_init(acc_full, 2);                                  // one multicast commit per issuing warp
+            ptx::mbar_init(acc_empty, 2 * EPI_WARPS);                     // epilogue warps of both CTAs
             ptx::fence_barrier_init();
         }
         __syncwarp();
-        ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+        ptx::tmem_alloc_pair<TMEM_COLS>(tmem_slot);
     }
     ptx::tc_fence_before();
     __syncthreads();
+    ptx::cluster_sync();     // the peer's barriers and tensor memory are set up before anyone arrives on them / issues pair MMAs
     ptx::tc_fence_after();
     // the CTA owns the SM and allocates all 512 columns, so the allocation starts at column 0 / lane 0: treating the base as
     // the constant 0 lets the compiler keep every TMEM address and descriptor of the MMA loop in uniform registers
@@ -191,6 +194,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     }
     ptx::tc_fence_before();
     __syncthreads();
+    ptx::cluster_sync();     // both CTAs' W is resident before the leader issues
     ptx::tc_fence_after();
 
     {
@@ -198,10 +202,11 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         const bool epi = warp < EPI_WARPS;
         // ---- loader geometry: this warp's chunk and, per piece i, the (row, plane) of the lane ----
         const int kc = warp / WPC, sub = warp % WPC;
-        auto piece_row = [&](int i) { return WPC == 1 ? (i & 1) * 32 + lane : (WPC == 2 ? sub * 32 + lane : sub * 16 + (lane & 15)); };
-        auto piece_plane = [&](int i) { return WPC == 1 ? (i >> 1) : (WPC == 2 ? i : 2 * i + (lane >> 4)); };
+        constexpr int NP = NKB / 2;                           // 16-byte pieces per lane and step: 32 rows x 8 planes x NKB chunks / 512
+        auto piece_row = [&](int i) { return WPC == 1 ? lane : (WPC == 2 ? sub * 16 + (lane & 15) : sub * 8 + (lane & 7)); };
+        auto piece_plane = [&](int i) { return WPC == 1 ? i : (WPC == 2 ? 2 * i + (lane >> 4) : 4 * i + (lane >> 3)); };
         const uint32_t sH_chunk = ptx::smem_u32(sH) + (uint32_t)(kc * H_BLK_BYTES);
-        const __nv_bfloat16* chunk_base = yx_tile + (size_t)kc * 8 * PLANE_STRIDE;
+        const __nv_bfloat16* chunk_base = yx_tile + (size_t)kc * 8 * PLANE_STRIDE + (size_t)(crank * ROWS_CTA) * PLANE_ELEMS;
 
         // ---- epilogue geometry ----
         const int q = warp & 3, half = (warp >> 2) & 1;       // TMEM lane quarter; utterance half (32 columns)
@@ -246,14 +251,14 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     }
                 }
                 if (threadIdx.x == 0) AVC_TRACE(0);
-                uint4 v[NKB];
+                uint4 v[NP];
 #pragma unroll
-                for (int i = 0; i < NKB; ++i)
+                for (int i = 0; i < NP; ++i)
                     v[i] = ld_strong(src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS);
                 // the MMAs of step t-1 still read the tiles until acc_full(t-1): normally long past
                 if (t >= 2 && !epi) ptx::mbar_wait(acc_full, (uint32_t)(t - 2) & 1);
 #pragma unroll
-                for (int i = 0; i < NKB; ++i) {
+                for (int i = 0; i < NP; ++i) {
                     const __nv_bfloat16* p = src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS;
                     uint32_t spin = 0;
                     while (unwritten(v[i])) {               // not written yet: poll again
@@ -268,35 +273,40 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 }
                 ptx::fence_proxy_async_smem();          // generic-proxy smem writes -> tcgen05.mma (async proxy) reads
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&gfull[warp >> 2]);
-                if (warp == MMA_WARP) {
-                    // the last loader warp issues the MMAs of the step, chunk by chunk in a fixed order (the accumulation
-                    // order must not depend on timing: results are bitwise reproducible).  Whole-warp, uniform operands.
-                    if (t >= 2) ptx::mbar_wait(acc_empty, (uint32_t)(t - 2) & 1);   // epilogue of step t-1 has read D
+                if (lane == 0) ptx::mbar_arrive_cluster(&gfull[warp >> 2], 0u);     // the LEADER's barrier (both CTAs arrive)
+                if (crank == 0 && warp >= MMA_WARP0) {
+                    // Leader CTA, warps 14/15: issue the pair's MMAs of the step, one K half each into its own accumulator,
+                    // chunk by chunk in a fixed order (the accumulation order must not depend on timing: results are bitwise
+                    // reproducible).  Whole-warp, uniform operands, one elected lane issues.
+                    const int ih = warp - MMA_WARP0;
+                    if (t >= 2) ptx::mbar_wait(acc_empty, (uint32_t)(t - 2) & 1);   // both epilogues of step t-1 have read D
+                    const uint32_t d_tmem = tmem_base + (uint32_t)(ih * TILE_N);
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
+                    for (int gg = 0; gg < 2; ++gg) {
+                        const int g = ih * 2 + gg;
                         ptx::mbar_wait(&gfull[g], (uint32_t)(t - 1) & 1);
                         ptx::tc_fence_after();
                         if (g == 0) AVC_TRACE(2);
 #pragma unroll
                         for (int cc = 0; cc < NKB / 4; ++cc) {
                             const int c = g * (NKB / 4) + cc;
+                            const uint32_t first = (gg | cc) == 0 ? 0u : 1u;
                             const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sH) + (uint32_t)(c * H_BLK_BYTES));
                             if (c < NKB_T) {
                                 const uint32_t a_tmem = tmem_base + W_COL0 + (uint32_t)(c * 32);
 #pragma unroll
                                 for (int k = 0; k < KBLK / 16; ++k)
-                                    ptx::umma_f16_ts_warp(tmem_base, a_tmem + (uint32_t)(k * 8), bdesc + (uint64_t)(k * 2), a.idesc, (c | k) != 0 ? 1u : 0u);
+                                    ptx::umma2_f16_ts_warp(d_tmem, a_tmem + (uint32_t)(k * 8), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
                             } else {
                                 const uint64_t adesc = ptx::umma_desc_sw128(ptx::smem_u32(sW + (c - NKB_T) * W_BLK_BYTES));
 #pragma unroll
                                 for (int k = 0; k < KBLK / 16; ++k)
-                                    ptx::umma_f16_warp(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, (c | k) != 0 ? 1u : 0u);
+                                    ptx::umma2_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
                             }
                         }
                     }
-                    ptx::umma_commit_warp(acc_full);
-                    AVC_TRACE(3);
+                    ptx::umma2_commit_warp(acc_full);       // -> acc_full of BOTH CTAs
+                    if (ih == 1) AVC_TRACE(3);
                 }
                 if (threadIdx.x == 0) AVC_TRACE(1);
             }
@@ -310,15 +320,17 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 ptx::mbar_wait(acc_full, (uint32_t)(t - 1) & 1);
                 if (threadIdx.x == 0) AVC_TRACE(4);
                 ptx::tc_fence_after();
-                uint32_t acc[2][16];
-                ptx::tmem_ld16(taddr, acc[0]);
-                ptx::tmem_ld16(taddr + 16, acc[1]);
+                uint32_t acc0[2][16], acc1[2][16];
+                ptx::tmem_ld16(taddr, acc0[0]);
+                ptx::tmem_ld16(taddr + 16, acc0[1]);
+                ptx::tmem_ld16(taddr + TILE_N, acc1[0]);
+                ptx::tmem_ld16(taddr + TILE_N + 16, acc1[1]);
                 ptx::tmem_ld_wait();
                 ptx::tc_fence_before();
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(acc_empty);
+                if (lane == 0) ptx::mbar_arrive_cluster(acc_empty, 0u);
 #pragma unroll
-                for (int k = 0; k < 32; ++k) act[k] = __uint_as_float(acc[k >> 4][k & 15]);
+                for (int k = 0; k < 32; ++k) act[k] = __uint_as_float(acc0[k >> 4][k & 15]) + __uint_as_float(acc1[k >> 4][k & 15]);
             } else {
 #pragma unroll
                 for (int k = 0; k < 32; ++k) act[k] = 0.0f;
@@ -384,9 +396,10 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 
     ptx::tc_fence_before();
     __syncthreads();
+    ptx::cluster_sync();     // no CTA may exit (or free tensor memory) while its peer can still arrive on its barriers
     if (warp == 0) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
+        ptx::tmem_dealloc_pair<TMEM_COLS>(tmem_base);
     }
 }
 
@@ -456,7 +469,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, i
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(Whh) failed: %d", (int)r); return bad(msg); }
     }
-    const int tiles_per_launch = num_sms / G_n;
+    const int tiles_per_launch = (num_sms & ~1) / G_n;
     const int rows_per_launch = tiles_per_launch * TILE_N;
     for (int bs = 0; bs < B; bs += rows_per_launch) {
         const int Bc = (B - bs) < rows_per_launch ? (B - bs) : rows_per_launch;
@@ -468,7 +481,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, i
         a.Y = reinterpret_cast<__nv_bfloat16*>(Y) + (size_t)bs * a.y_sb;
         a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
         a.tiles = ceil_div(B, TILE_N); a.tile0 = bs / TILE_N;
-        a.idesc = ptx::umma_idesc_f16(1, MROWS, TILE_N);
+        a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, TILE_N);      // the pair's MMA: M = 256 (128 gate rows per CTA), N = 64
         plan->args.push_back(a);
         plan->grids.push_back(dim3(G_n, ceil_div(Bc, TILE_N)));
     }
@@ -492,9 +505,11 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
         // cooperative launch: CTAs wait on one another's output, so co-residency must be guaranteed
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = plan->grids[i]; cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = (size_t)plan->smem_bytes; cfg.stream = s;
-        cudaLaunchAttribute at[1];
+        cudaLaunchAttribute at[2];
         at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
-        cfg.attrs = at; cfg.numAttrs = 1;
+        at[1].id = cudaLaunchAttributeClusterDimension;      // CTA pairs: adjacent unit slices of one batch tile
+        at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 2;
         e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb), kargs);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;

@@ -73,7 +73,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp: provably uniform
     const int num_kb = a.taps * a.kblocks_per_tap;
 
     if (warp == 0 && lane == 0) {
@@ -90,49 +90,46 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            int stage = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-                const int nt = tile % a.tiles_n, mt = tile / a.tiles_n;
-                const int t0 = (mt % a.tiles_t) * a.TB, b0 = (mt / a.tiles_t) * a.BB;
-                const int n0 = nt * BLOCK_N;
-                for (int tap = 0; tap < a.taps; ++tap) {
-                    for (int kc = 0; kc < a.kblocks_per_tap; ++kc) {
-                        ptx::mbar_wait(&empty[stage], phase ^ 1);
-                        ptx::mbar_expect_tx(&full[stage], C::STAGE_BYTES);
-                        ptx::tma_load_3d(sA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BLOCK_K, t0 + tap - a.pad, b0);
-                        ptx::tma_load_2d(sW + stage * C::W_STAGE_BYTES, &tmW, &full[stage], tap * a.Cp + kc * BLOCK_K, n0);
-                        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
-                    }
+        // ===================== TMA producer (whole warp, uniform operands, one elected lane issues) =====================
+        int stage = 0; uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+            const int nt = tile % a.tiles_n, mt = tile / a.tiles_n;
+            const int t0 = (mt % a.tiles_t) * a.TB, b0 = (mt / a.tiles_t) * a.BB;
+            const int n0 = nt * BLOCK_N;
+            for (int tap = 0; tap < a.taps; ++tap) {
+                for (int kc = 0; kc < a.kblocks_per_tap; ++kc) {
+                    ptx::mbar_wait(&empty[stage], phase ^ 1);
+                    ptx::mbar_expect_tx_warp(&full[stage], C::STAGE_BYTES);
+                    ptx::tma_load_3d_warp(sA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BLOCK_K, t0 + tap - a.pad, b0);
+                    ptx::tma_load_2d_warp(sW + stage * C::W_STAGE_BYTES, &tmW, &full[stage], tap * a.Cp + kc * BLOCK_K, n0);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            int stage = 0; uint32_t phase = 0;
-            int as = 0; uint32_t aphase = 0;
-            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-                ptx::mbar_wait(&tempty[as], aphase ^ 1);
+        // ===================== MMA issuer (whole warp, uniform operands, one elected lane issues) =====================
+        // an `if (lane == 0)` around the loop makes the compiler wrap every UTCHMMA in an ELECT/R2UR/BRA.U.ANY loop
+        int stage = 0; uint32_t phase = 0;
+        int as = 0; uint32_t aphase = 0;
+        for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+            ptx::mbar_wait(&tempty[as], aphase ^ 1);
+            ptx::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(as * C::ACC_STRIDE);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                ptx::mbar_wait(&full[stage], phase);
                 ptx::tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(as * C::ACC_STRIDE);
-                for (int kb = 0; kb < num_kb; ++kb) {
-                    ptx::mbar_wait(&full[stage], phase);
-                    ptx::tc_fence_after();
-                    const uint64_t adesc = ptx::umma_desc_sw128(ptx::smem_u32(sA + stage * A_STAGE_BYTES));
-                    const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sW + stage * C::W_STAGE_BYTES));
+                const uint64_t adesc = ptx::umma_desc_sw128(ptx::smem_u32(sA + stage * A_STAGE_BYTES));
+                const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sW + stage * C::W_STAGE_BYTES));
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        // advance 32 bytes (16 elements) along K inside the swizzle row: +2 in the (addr>>4) field
-                        ptx::umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, (kb | k) != 0 ? 1u : 0u);
-                    }
-                    ptx::umma_commit(&empty[stage]);
-                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                    // advance 32 bytes (16 elements) along K inside the swizzle row: +2 in the (addr>>4) field
+                    ptx::umma_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, (kb | k) != 0 ? 1u : 0u);
                 }
-                ptx::umma_commit(&tfull[as]);
-                if (++as == 2) { as = 0; aphase ^= 1; }
+                ptx::umma_commit_warp(&empty[stage]);
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
             }
+            ptx::umma_commit_warp(&tfull[as]);
+            if (++as == 2) { as = 0; aphase ^= 1; }
         }
     } else {
         // ===================== epilogue (warps 2..5) =====================
