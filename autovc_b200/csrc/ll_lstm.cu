@@ -81,6 +81,8 @@ struct LlLstmArgs {
     long long y_sb, y_st;        // element strides of Y along utterance / frame
     long long gx_sb, gx_st;      // same for Gx rows (frame index t / gx_div)
     uint32_t idesc;
+    int approx;                  // 1 (default): gate activations with MUFU.TANH (tanh.approx.f32, abs err ~5e-4: below the bf16 rounding of h;
+                                 // measured end-to-end error unchanged); AVC_LSTM_EXACT=1 selects ex2/rcp based sigmoid/tanh
     long long* trace;            // optional clock64 trace of CTA (0,0) (AVC_LSTM_TRACE=1), nullptr normally
 };
 
@@ -242,7 +244,8 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             if (t >= 1) {
                 // ---- h_{t-1} chunk: L2 -> registers (poll) -> swizzled operand tile in shared memory ----
                 const __nv_bfloat16* src = chunk_base + (size_t)(t - 1) * step_elems;
-                {   // step start: poll one 16-byte canary per lane; whole-chunk polls would compete with the producers' stores
+                {   // step start: poll one 16-byte canary per lane; whole-chunk polls would compete with the producers' stores.
+                    // (Several staggered polls in flight were measured slower: the data has usually landed when a warp gets here.)
                     const __nv_bfloat16* p = src + (size_t)piece_plane(0) * PLANE_STRIDE + piece_row(0) * PLANE_ELEMS;
                     uint4 cn = ld_strong(p);
                     for (uint32_t spin = 0; unwritten(cn); ++spin) {
@@ -336,11 +339,24 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 for (int k = 0; k < 32; ++k) act[k] = 0.0f;
             }
             // + Gx_t[utterance half*32 + k][gate row R], then this lane's activation
+            if (a.approx) {
+                // sigmoid(x) = 0.5 tanh(0.5 x) + 0.5, tanh(x) as is: one MUFU.TANH per gate value
+                const float ps = gj == 2 ? 1.0f : 0.5f, po = gj == 2 ? 0.0f : 0.5f;
 #pragma unroll
-            for (int k = 0; k < 32; ++k) {
-                const float x = act[k] + ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
-                act[k] = __fdividef(act_s, 1.0f + __expf(-act_s * x)) + act_o;
+                for (int k = 0; k < 32; ++k) {
+                    const float x = act[k] + ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
+                    float th;
+                    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(ps * x));
+                    act[k] = fmaf(ps, th, po);
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 32; ++k) {
+                    const float x = act[k] + ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
+                    act[k] = __fdividef(act_s, 1.0f + __expf(-act_s * x)) + act_o;
+                }
             }
+            if (threadIdx.x == 0) AVC_TRACE(6);
             // 4x4 quad transpose (blocks of 8 columns): lane j ends with all four gates of columns 8j..8j+7
             float X[16], Y2[16];
 #pragma unroll
@@ -365,11 +381,15 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     const float ig = (gj & 2) ? e2 : e0, gg = (gj & 2) ? e0 : e2;
                     const float fg = (gj & 2) ? e3 : e1, og = (gj & 2) ? e1 : e3;
                     c[kk] = fg * c[kk] + ig * gg;
-                    hv[w] = og * (1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * c[kk])));
+                    float tc;
+                    if (a.approx) asm("tanh.approx.f32 %0, %1;" : "=f"(tc) : "f"(c[kk]));
+                    else tc = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * c[kk]));
+                    hv[w] = og * tc;
                 }
                 __nv_bfloat162 h2 = __floats2bfloat162_rn(hv[0], hv[1]);
                 hp[k >> 1] = *reinterpret_cast<uint32_t*>(&h2);
             }
+            if (threadIdx.x == 0) AVC_TRACE(7);
             // transpose through shared memory: hT[utterance][unit], 16-byte pieces XOR-swizzled by (utterance / 8) & 3
             {
                 const int unit = q * 8 + (lane >> 2);
@@ -382,6 +402,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 }
             }
             named_bar_sync(1, EPI_THREADS);
+            if (threadIdx.x == 0) AVC_TRACE(8);
             {
                 const uint4 hv4 = ld_shared_v4(ht_smem + (uint32_t)(ou * 64 + ((op ^ ((ou >> 3) & 3)) << 4)));
                 // utterances beyond B hold bounded garbage: they are exchanged like any other row, so loaders need no
@@ -481,6 +502,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, i
         a.Y = reinterpret_cast<__nv_bfloat16*>(Y) + (size_t)bs * a.y_sb;
         a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
         a.tiles = ceil_div(B, TILE_N); a.tile0 = bs / TILE_N;
+        a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
         a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, TILE_N);      // the pair's MMA: M = 256 (128 gate rows per CTA), N = 64
         plan->args.push_back(a);
         plan->grids.push_back(dim3(G_n, ceil_div(Bc, TILE_N)));
@@ -518,13 +540,14 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
             cudaStreamSynchronize(s);
             cudaMemcpy(hbuf, d_trace, sizeof hbuf, cudaMemcpyDeviceToHost);
             fprintf(stderr, "ll_lstm trace H=%d B=%d grid=(%d,%d): cycles since warp 0 saw its canary: "
-                    "warp0_done warp0_mma_issue warp0_mma_issued acc_seen h_stored | step period\n",
+                    "warp0_done mma_issue_start mma_issued acc_seen h_stored (activations cell_update staged) | step period\n",
                     args.H, args.B, plan->grids[i].x, plan->grids[i].y);
             for (int st = 0; st < TRACE_STEPS; ++st) {
                 const long long* r = hbuf + st * TRACE_PTS;
                 if (!r[0]) continue;
                 fprintf(stderr, "  t=%d:", TRACE_T0 + st);
                 for (int p = 1; p <= 5; ++p) fprintf(stderr, " %6lld", r[p] - r[0]);
+                fprintf(stderr, " (%lld %lld %lld)", r[6] - r[0], r[7] - r[0], r[8] - r[0]);
                 if (st + 1 < TRACE_STEPS && r[TRACE_PTS]) fprintf(stderr, " | %6lld", r[TRACE_PTS] - r[0]);
                 fprintf(stderr, "\n");
             }
