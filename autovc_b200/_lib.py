@@ -21,7 +21,8 @@ AVC_PREC_BF16 = 0
 AVC_PREC_FP32 = 1
 
 EXPORTS = ["avc_abi_version", "avc_create", "avc_load_weights", "avc_workspace_bytes", "avc_forward", "avc_encode",
-           "avc_last_launch_count", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error"]
+           "avc_last_launch_count", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error",
+           "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_reduce"]
 
 
 class AvcDims(Structure):
@@ -67,6 +68,14 @@ def lib() -> ctypes.CDLL:
     L.avc_debug_gemm.argtypes = [c_void_p, c_char_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int,
                                  c_int, c_void_p, c_void_p, c_void_p]
     L.avc_debug_gemm.restype = c_int
+    L.avc_se_load_weights.argtypes = [c_void_p, POINTER(AvcWeightDesc), c_int]
+    L.avc_se_load_weights.restype = c_int
+    L.avc_se_workspace_bytes.argtypes = [c_void_p, c_int, c_int]
+    L.avc_se_workspace_bytes.restype = c_size_t
+    L.avc_se_forward.argtypes = [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]
+    L.avc_se_forward.restype = c_int
+    L.avc_se_reduce.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]
+    L.avc_se_reduce.restype = c_int
     L.avc_destroy.argtypes = [c_void_p]
     L.avc_destroy.restype = None
     L.avc_last_error.argtypes = [c_void_p]

@@ -37,8 +37,13 @@ enum LayerId {
     L_DEC_L2_0_IH, L_DEC_L2_0_HH, L_DEC_L2_1_IH, L_DEC_L2_1_HH,
     L_DEC_LINEAR,
     L_POST_CONV0, L_POST_CONV1, L_POST_CONV2, L_POST_CONV3, L_POST_CONV4,
+    L_GEN_COUNT,
+    // d-vector speaker encoder (reference autovc/speaker_encoder/model.py:48-58): LSTM(40,256,3) + Linear(256,256)
+    L_SE_L0_IH = L_GEN_COUNT, L_SE_L0_HH, L_SE_L1_IH, L_SE_L1_HH, L_SE_L2_IH, L_SE_L2_HH, L_SE_LINEAR,
     L_COUNT
 };
+
+constexpr int SE_MELS = 40, SE_H = 256, SE_LAYERS = 3, SE_EMB = 256;   // reference utils/hparams.py:60-63, model.py:48-58
 
 const char* kLayerNames[L_COUNT] = {
     "enc.conv0", "enc.conv1", "enc.conv2",
@@ -48,6 +53,7 @@ const char* kLayerNames[L_COUNT] = {
     "dec.lstm2.l0.ih", "dec.lstm2.l0.hh", "dec.lstm2.l1.ih", "dec.lstm2.l1.hh",
     "dec.linear",
     "post.conv0", "post.conv1", "post.conv2", "post.conv3", "post.conv4",
+    "se.lstm.l0.ih", "se.lstm.l0.hh", "se.lstm.l1.ih", "se.lstm.l1.hh", "se.lstm.l2.ih", "se.lstm.l2.hh", "se.linear",
 };
 
 struct Workspace {
@@ -67,6 +73,7 @@ struct avc_ctx {
     int precision = AVC_PREC_BF16;
     int num_sms = 148;
     bool loaded = false;
+    bool se_loaded = false;    // avc_se_load_weights completed
     bool force_simt = false;   // AVC_FORCE_SIMT=1: debugging aid, run the GEMMs of the bf16 mode on the CUDA cores
     std::string err = "";
     std::map<std::string, std::vector<float>> raw;
@@ -80,7 +87,7 @@ struct avc_ctx {
     bool simt_lstm = false;    // AVC_SIMT_LSTM=1: debugging aid, per-step CUDA-core recurrences in the bf16 mode
     int plan_B = 0, plan_T = 0;
     void* plan_ws = nullptr;
-    bool plan_encode_only = false;
+    int plan_mode = 0;         // 0 forward, 1 encode only, 2 speaker encoder
     // optional per-phase timing (avc_set_profiling): events at phase boundaries of the last run
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;
@@ -382,7 +389,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     for (auto ev : h->prof_events) cudaEventDestroy(ev);
     h->prof_events.clear(); h->prof_cats.clear();
     if (r.use_tc()) {
-        const bool hit = h->plan_ws == workspace && h->plan_B == B && h->plan_T == T && h->plan_encode_only == encode_only && !h->plans.empty();
+        const bool hit = h->plan_ws == workspace && h->plan_B == B && h->plan_T == T && h->plan_mode == (encode_only ? 1 : 0) && !h->plans.empty();
         if (!hit) {
             for (auto* p : h->plans) tc_gemm_plan_destroy(p);
             h->plans.clear();
@@ -391,7 +398,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
             for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
             h->llplans.clear();
             r.building_plans = true;
-            h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_encode_only = encode_only;
+            h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_mode = encode_only ? 1 : 0;
         }
     }
 
@@ -459,6 +466,86 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     return r.rc;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// d-vector speaker encoder (reference autovc/speaker_encoder/model.py:70-90): same GEMM + recurrence kernels
+// ---------------------------------------------------------------------------------------------
+struct SeWorkspace { char* Xp; float* Gx; char* Ya; char* Yb2; float* E; Workspace lstm; size_t total; };
+
+SeWorkspace carve_se(const avc_ctx* h, char* base, int N, int T) {
+    const size_t as = dtype_size(act_type(h));
+    const size_t M = (size_t)N * T;
+    SeWorkspace w{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align256(bytes); return p; };
+    w.Xp = take(M * round_up(SE_MELS, 16) * as);
+    w.Gx = (float*)take(M * 4 * SE_H * 4);
+    w.Ya = take(M * SE_H * as);
+    w.Yb2 = take(M * SE_H * as);
+    w.E = (float*)take((size_t)N * SE_EMB * 4);
+    w.lstm.cstate = (float*)take((size_t)2 * N * SE_H * 4);
+    w.lstm.ready_bytes = (size_t)tc_lstm_ready_words(N, T) * 4;
+    w.lstm.ready = (unsigned int*)take(w.lstm.ready_bytes);
+    w.lstm.Yb = take(tc_lstm_tile_bytes(N, T, SE_H));
+    w.total = off;
+    return w;
+}
+
+int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!h) return AVC_ERR_INVALID_ARG;
+    if (h->device < 0) return fail(h, AVC_ERR_INVALID_ARG, "host-only context (device=-1) cannot run");
+    if (!h->se_loaded) return fail(h, AVC_ERR_NOT_LOADED, "avc_se_load_weights has not completed");
+    if (!partials || !embeds || N <= 0 || T <= 0) return fail(h, AVC_ERR_INVALID_ARG, "null pointer or non-positive N/T");
+    SeWorkspace w = carve_se(h, (char*)workspace, N, T);
+    if (!workspace || workspace_bytes < w.total || ((uintptr_t)workspace & 255))
+        return fail(h, AVC_ERR_WORKSPACE, "workspace must be 256-byte aligned and >= %zu bytes (got %zu)", w.total, workspace_bytes);
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+
+    Runner r{h, (cudaStream_t)stream, N, T};
+    r.wsp = &w.lstm;
+    h->launches = 0;
+    for (auto ev : h->prof_events) cudaEventDestroy(ev);
+    h->prof_events.clear(); h->prof_cats.clear();
+    if (r.use_tc()) {
+        const bool hit = h->plan_ws == workspace && h->plan_B == N && h->plan_T == T && h->plan_mode == 2 && !h->plans.empty();
+        if (!hit) {
+            for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+            h->plans.clear();
+            for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
+            h->lplans.clear();
+            for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
+            h->llplans.clear();
+            r.building_plans = true;
+            h->plan_ws = workspace; h->plan_B = N; h->plan_T = T; h->plan_mode = 2;
+        }
+    }
+    const int at = act_type(h);
+    const int M = N * T, Kp = round_up(SE_MELS, 16);
+    r.check(launch_cast_pad_rows(partials, w.Xp, at, (long long)M, SE_MELS, Kp, r.s), "cast partials"); h->launches++;
+    char* in = w.Xp; int ldin = Kp;
+    char* bufs[2] = {w.Ya, w.Yb2};
+    for (int l = 0; l < SE_LAYERS; ++l) {
+        r.gemm(L_SE_L0_IH + 2 * l, in, at, ldin, M, T, ACT_NONE, w.Gx, DT_F32, 4 * SE_H);
+        r.lstm(L_SE_L0_HH + 2 * l, w.Gx, T, 1, bufs[l & 1], at, SE_H, 1);
+        in = bufs[l & 1]; ldin = SE_H;
+    }
+    // hidden[-1] = last layer's h at the final frame (model.py:83-85): rows of pitch T*H starting at frame T-1
+    const char* h_last = in + (size_t)(T - 1) * SE_H * dtype_size(at);
+    r.gemm(L_SE_LINEAR, h_last, at, T * SE_H, N, 1, ACT_RELU, w.E, DT_F32, SE_EMB);
+    r.check(launch_l2norm_rows(w.E, embeds, N, SE_EMB, r.s), "l2 normalise"); h->launches++;
+    if (!r.ok() && r.building_plans) {
+        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+        h->plans.clear();
+        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
+        h->lplans.clear();
+        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
+        h->llplans.clear();
+        h->plan_ws = nullptr;
+    }
+    return r.rc;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -466,7 +553,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
 // ---------------------------------------------------------------------------------------------
 extern "C" {
 
-int avc_abi_version(void) { return 1; }
+int avc_abi_version(void) { return 2; }
 
 int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision) {
     if (!out || !dims) return fail(nullptr, AVC_ERR_INVALID_ARG, "null out/dims");
@@ -537,14 +624,14 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
     ok = ok && pack_conv(h, L[L_POST_CONV4], "postnet.convolutions.4", CONV_CH, N_MELS);
     if (!ok) { h->loaded = false; return AVC_ERR_MISSING_WEIGHT; }
     h->raw.clear();
-    for (int i = 0; i < L_COUNT; ++i) {
+    for (int i = 0; i < L_GEN_COUNT; ++i) {
         const bool post = i >= L_POST_CONV0;
         L[i].w_type = h->precision == AVC_PREC_FP32 ? DT_F32 : (post ? DT_F16 : DT_BF16);
     }
     if (h->device >= 0) {
         cudaError_t e = cudaSetDevice(h->device);
         if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
-        for (int i = 0; i < L_COUNT; ++i) {
+        for (int i = 0; i < L_GEN_COUNT; ++i) {
             int rc = upload_layer(h, L[i]);
             if (rc != AVC_OK) return rc;
         }
@@ -639,6 +726,62 @@ int avc_debug_gemm(avc_handle h, const char* layer, int use_tc, const void* A, i
         return AVC_OK;
     }
     return fail(h, AVC_ERR_INVALID_ARG, "unknown layer '%s'", layer);
+}
+
+int avc_se_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
+    if (!h || !table || n <= 0) return fail(h, AVC_ERR_INVALID_ARG, "null handle/table");
+    h->se_loaded = false;
+    h->raw.clear();
+    for (int i = 0; i < n; ++i) {
+        if (!table[i].name || !table[i].data || table[i].numel < 0) return fail(h, AVC_ERR_INVALID_ARG, "weight table entry %d is malformed", i);
+        h->raw[table[i].name].assign(table[i].data, table[i].data + table[i].numel);
+    }
+    Layer* L = h->layers;
+    bool ok = true;
+    for (int l = 0; l < SE_LAYERS; ++l)
+        ok = ok && pack_lstm(h, L[L_SE_L0_IH + 2 * l], L[L_SE_L0_HH + 2 * l], "lstm", l, l == 0 ? SE_MELS : SE_H, SE_H, false);
+    ok = ok && pack_linear(h, L[L_SE_LINEAR], "linear", SE_H, SE_EMB);
+    h->raw.clear();
+    if (!ok) return AVC_ERR_MISSING_WEIGHT;
+    for (int i = L_SE_L0_IH; i < L_COUNT; ++i) L[i].w_type = h->precision == AVC_PREC_FP32 ? DT_F32 : DT_BF16;
+    if (h->device >= 0) {
+        cudaError_t e = cudaSetDevice(h->device);
+        if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+        for (int i = L_SE_L0_IH; i < L_COUNT; ++i) {
+            int rc = upload_layer(h, L[i]);
+            if (rc != AVC_OK) return rc;
+        }
+        if (h->plan_mode == 2) {   // cached speaker-encoder plans point at the old weight buffers
+            for (auto* p : h->plans) tc_gemm_plan_destroy(p);
+            h->plans.clear();
+            for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
+            h->lplans.clear();
+            for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
+            h->llplans.clear();
+            h->plan_ws = nullptr;
+        }
+    }
+    h->se_loaded = true;
+    return AVC_OK;
+}
+
+size_t avc_se_workspace_bytes(avc_handle h, int N, int T) {
+    if (!h || N <= 0 || T <= 0) return 0;
+    return carve_se(h, nullptr, N, T).total;
+}
+
+int avc_se_forward(avc_handle h, const float* partials, int N, int T, float* embeds, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+    return run_se(h, partials, N, T, embeds, workspace, workspace_bytes, stream);
+}
+
+int avc_se_reduce(avc_handle h, const float* embeds, const int32_t* offsets, int S, float* speaker_embeds, void* stream) {
+    if (!h || !embeds || !offsets || !speaker_embeds || S <= 0) return fail(h, AVC_ERR_INVALID_ARG, "null pointer or S <= 0");
+    if (h->device < 0) return fail(h, AVC_ERR_INVALID_ARG, "host-only context (device=-1) cannot run");
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e == cudaSuccess) e = launch_segment_mean_renorm(embeds, offsets, speaker_embeds, S, SE_EMB, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "segment mean: %s", cudaGetErrorString(e));
+    return AVC_OK;
 }
 
 void avc_destroy(avc_handle h) {

@@ -12,6 +12,11 @@ cudaError_t launch_pack_input(const float* x, const float* c_org, void* X0, int 
 cudaError_t launch_codes(const float* Y, const float* c_trg, float* codes, void* D, int d_type, int B, int T, int dn,
                          int E, int freq, cudaStream_t s);
 
+// speaker-encoder helpers (simt_kernels.cu)
+cudaError_t launch_cast_pad_rows(const float* in, void* out, int out_type, long long rows, int K, int Kp, cudaStream_t s);
+cudaError_t launch_l2norm_rows(const float* in, float* out, int rows, int D, cudaStream_t s);
+cudaError_t launch_segment_mean_renorm(const float* emb, const int* offsets, float* out, int S, int D, cudaStream_t s);
+
 // tc_gemm.cu (tcgen05 + TMA implicit-GEMM)
 struct TcGemmPlan;  // opaque: tensor maps + tiling for one (layer, B, T) instance
 // Returns nullptr and sets *err when the shape is not supported by the tensor-core kernel.

@@ -321,4 +321,71 @@ cudaError_t launch_codes(const float* Y, const float* c_trg, float* codes, void*
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// d-vector speaker encoder helpers (reference autovc/speaker_encoder/model.py:70-90, 185-186)
+// ---------------------------------------------------------------------------------------------
+template <typename TO>
+__global__ void cast_pad_rows_kernel(const float* __restrict__ in, TO* __restrict__ out, long long rows, int K, int Kp) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * Kp) return;
+    const long long r = i / Kp; const int k = (int)(i - r * Kp);
+    const float v = k < K ? in[r * K + k] : 0.0f;
+    if constexpr (sizeof(TO) == 4) out[i] = v;
+    else out[i] = TO(v);
+}
+
+// out[r, :] = in[r, :] / ||in[r, :]||_2 ; one warp per row
+__global__ void l2norm_rows_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int D) {
+    const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= rows) return;
+    float ss = 0.0f;
+    for (int d = lane; d < D; d += 32) { const float v = in[(size_t)r * D + d]; ss += v * v; }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float inv = 1.0f / sqrtf(ss);
+    for (int d = lane; d < D; d += 32) out[(size_t)r * D + d] = in[(size_t)r * D + d] * inv;
+}
+
+// speaker s: mean of its partial embeddings rows [off[s], off[s+1]), re-normalised (embed_utterance, model.py:185-186)
+__global__ void segment_mean_renorm_kernel(const float* __restrict__ emb, const int* __restrict__ off, float* __restrict__ out, int D) {
+    extern __shared__ float sh[];
+    const int s = blockIdx.x, lo = off[s], hi = off[s + 1];
+    float ss = 0.0f;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        float a = 0.0f;
+        for (int r = lo; r < hi; ++r) a += emb[(size_t)r * D + d];
+        a /= (float)(hi - lo);
+        sh[d] = a;
+        ss += a * a;
+    }
+    __shared__ float red[32];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.0f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += red[w];
+    const float inv = 1.0f / sqrtf(tot);
+    for (int d = threadIdx.x; d < D; d += blockDim.x) out[(size_t)s * D + d] = sh[d] * inv;
+}
+
+cudaError_t launch_cast_pad_rows(const float* in, void* out, int out_type, long long rows, int K, int Kp, cudaStream_t s) {
+    const long long n = rows * Kp;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (out_type == DT_F32) cast_pad_rows_kernel<float><<<grid, 256, 0, s>>>(in, (float*)out, rows, K, Kp);
+    else if (out_type == DT_BF16) cast_pad_rows_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(in, (__nv_bfloat16*)out, rows, K, Kp);
+    else cast_pad_rows_kernel<__half><<<grid, 256, 0, s>>>(in, (__half*)out, rows, K, Kp);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_l2norm_rows(const float* in, float* out, int rows, int D, cudaStream_t s) {
+    l2norm_rows_kernel<<<ceil_div(rows, 8), 256, 0, s>>>(in, out, rows, D);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_segment_mean_renorm(const float* emb, const int* offsets, float* out, int S, int D, cudaStream_t s) {
+    segment_mean_renorm_kernel<<<S, 256, D * sizeof(float), s>>>(emb, offsets, out, D);
+    return cudaGetLastError();
+}
+
 }  // namespace avc

@@ -34,7 +34,8 @@ class Engine:
         _ENGINES[self.id] = self
 
     # -- weights -----------------------------------------------------------------------------
-    def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+    def load_state_dict(self, sd: Dict[str, torch.Tensor], speaker_encoder: bool = False) -> None:
+        """Hand a state dict to avc_load_weights (generator) or avc_se_load_weights (d-vector speaker encoder)."""
         keep, names = [], []
         for k, v in sd.items():
             if not v.is_floating_point():
@@ -46,7 +47,8 @@ class Engine:
             table[i].name = n
             table[i].data = ctypes.cast(t.data_ptr(), ctypes.POINTER(ctypes.c_float))
             table[i].numel = t.numel()
-        L.raise_for(L.lib().avc_load_weights(self._h, table, len(keep)), self._h)
+        load = L.lib().avc_se_load_weights if speaker_encoder else L.lib().avc_load_weights
+        L.raise_for(load(self._h, table, len(keep)), self._h)
 
     def packed(self, which: str) -> torch.Tensor:
         n = L.lib().avc_debug_packed(self._h, which.encode(), None, 0)
@@ -91,6 +93,39 @@ class Engine:
                                  post.data_ptr(), codes.data_ptr(), ws.data_ptr(), ws.numel(), stream)
         L.raise_for(rc, self._h)
         return mel, post, codes
+
+    # -- d-vector speaker encoder ----------------------------------------------------------------
+    def se_forward(self, partials: torch.Tensor) -> torch.Tensor:
+        """partials (N,T,40) float32 CUDA -> unit-norm embeddings (N,256) (avc_se_forward)."""
+        N, T, C = partials.shape
+        if C != 40:
+            raise RuntimeError(f"speaker encoder expects (N, n_frames, 40) mel filterbanks, got {tuple(partials.shape)}")
+        dev = partials.device
+        out = torch.empty(N, 256, dtype=torch.float32, device=dev)
+        if N == 0:
+            return out
+        if T == 0:
+            raise ValueError("speaker encoder needs at least one frame")
+        need = int(L.lib().avc_se_workspace_bytes(self._h, N, T))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = None
+            self._ws = torch.empty(need, dtype=torch.uint8, device=torch.device("cuda", self.device_index))
+        stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        rc = L.lib().avc_se_forward(self._h, partials.data_ptr(), N, T, out.data_ptr(), self._ws.data_ptr(),
+                                    self._ws.numel(), stream)
+        L.raise_for(rc, self._h)
+        return out
+
+    def se_reduce(self, embeds: torch.Tensor, offsets: torch.Tensor) -> torch.Tensor:
+        """embeds (N,256) float32, offsets (S+1,) int32, both CUDA -> (S,256): mean of each row segment, renormalised."""
+        S = offsets.numel() - 1
+        out = torch.empty(S, 256, dtype=torch.float32, device=embeds.device)
+        if S <= 0:
+            return out
+        stream = ctypes.c_void_p(torch.cuda.current_stream(embeds.device).cuda_stream)
+        rc = L.lib().avc_se_reduce(self._h, embeds.data_ptr(), offsets.data_ptr(), S, out.data_ptr(), stream)
+        L.raise_for(rc, self._h)
+        return out
 
     _DT = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
 
@@ -143,6 +178,7 @@ class Engine:
 _lib_def = torch.library.Library("autovc_b200", "DEF")
 _lib_def.define("generator_forward(Tensor x, Tensor c_org, Tensor c_trg, int engine) -> (Tensor, Tensor, Tensor)")
 _lib_def.define("generator_encode(Tensor x, Tensor c_org, int engine) -> Tensor")
+_lib_def.define("speaker_embed(Tensor partials, int engine) -> Tensor")
 
 
 def _prep(t: torch.Tensor) -> torch.Tensor:
@@ -157,13 +193,19 @@ def _encode_cuda(x, c_org, engine: int):
     return _ENGINES[engine].forward(_prep(x), _prep(c_org), None)
 
 
+def _speaker_embed_cuda(partials, engine: int):
+    return _ENGINES[engine].se_forward(_prep(partials))
+
+
 def _no_cpu(*_a, **_k):
-    raise RuntimeError("autovc_b200::generator_forward has only a CUDA (sm_100a) implementation; there is no CPU fallback")
+    raise RuntimeError("autovc_b200 ops have only a CUDA (sm_100a) implementation; there is no CPU fallback")
 
 
 _lib_impl_cuda = torch.library.Library("autovc_b200", "IMPL", "CUDA")
 _lib_impl_cuda.impl("generator_forward", _forward_cuda)
 _lib_impl_cuda.impl("generator_encode", _encode_cuda)
+_lib_impl_cuda.impl("speaker_embed", _speaker_embed_cuda)
 _lib_impl_cpu = torch.library.Library("autovc_b200", "IMPL", "CPU")
 _lib_impl_cpu.impl("generator_forward", _no_cpu)
 _lib_impl_cpu.impl("generator_encode", _no_cpu)
+_lib_impl_cpu.impl("speaker_embed", _no_cpu)

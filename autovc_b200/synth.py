@@ -117,3 +117,22 @@ def synth_inputs(batch: int, frames: int, seed: int = 1234, dim_emb: int = 256, 
     c_org = emb()
     c_trg = c_org.copy() if same_speaker else emb()
     return torch.from_numpy(x), torch.from_numpy(c_org), torch.from_numpy(c_trg)
+
+
+def synth_speaker_encoder(seed: int = 5, n_partials: int = 8, n_frames: int = 160):
+    """Seeded d-vector speaker-encoder weights (reference names, `speaker_encoder/model.py:48-58`) and a batch of
+    partial utterances (n_partials, n_frames, 40).  The draw order is the one `oracle/make_golden.py` used for
+    `tests/golden/speaker_encoder_p8.npz` (seed 5, 8 partials of 160 frames)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    names = []
+    for l in range(3):
+        names += [f"lstm.weight_ih_l{l}", f"lstm.weight_hh_l{l}", f"lstm.bias_ih_l{l}", f"lstm.bias_hh_l{l}"]
+    names += ["linear.weight", "linear.bias"]
+    shapes = {"lstm.weight_ih_l0": (1024, 40), "linear.weight": (256, 256), "linear.bias": (256,)}
+    sd = {}
+    for n in names:
+        shp = shapes.get(n, (1024, 256) if "weight" in n else (1024,))
+        sd[n] = torch.from_numpy(rng.uniform(-1 / 16, 1 / 16, size=shp).astype(np.float32))
+    parts = torch.from_numpy(rng.normal(size=(n_partials, n_frames, 40)).astype(np.float32))
+    return sd, parts

@@ -123,13 +123,35 @@ int64_t avc_debug_packed(avc_handle h, const char* which, float* out, int64_t ca
 int avc_debug_gemm(avc_handle h, const char* layer, int use_tc, const void* A, int a_type, int lda, int M, int T, int act,
                    void* out, int out_type, int ldo, float* out_t, const float* res_t, void* stream);
 
+/* ---- d-vector speaker encoder: the producer of c_org / c_trg -------------------------------
+ * Replaces SpeakerEncoder.forward (reference autovc/speaker_encoder/model.py:70-90):
+ *     LSTM(40, 256, 3 layers, batch_first) -> final h of the last layer -> relu(Linear(256,256)) -> L2 normalise
+ * and the partial-utterance averaging of embed_utterance (model.py:185-186).  The weights live in the same handle as
+ * the generator's; state-dict names as the reference module has them: "lstm.weight_ih_l0" [1024,40],
+ * "lstm.weight_hh_l0" [1024,256], "lstm.bias_ih_l0", "lstm.bias_hh_l0" [1024] (likewise l1, l2 with K = 256),
+ * "linear.weight" [256,256], "linear.bias" [256].  Other entries (similarity_weight/bias) are ignored. */
+int avc_se_load_weights(avc_handle h, const avc_weight_desc* table, int n);
+
+/* Bytes of device scratch avc_se_forward needs for N partial utterances of T frames.  0 on error. */
+size_t avc_se_workspace_bytes(avc_handle h, int N, int T);
+
+/* SpeakerEncoder.forward (model.py:70-90).  Device pointers: partials [N,T,40] float32 (batch_first, the reference's
+ * (batch, n_frames, n_channels)), embeds [N,256] float32 unit-norm rows.  The reference runs one utterance's partials
+ * per call (model.py:141 "TODO: handle multiple wavs"); here N may span all partials of all speakers of a work list. */
+int avc_se_forward(avc_handle h, const float* partials, int N, int T, float* embeds, void* workspace,
+                   size_t workspace_bytes, void* stream);
+
+/* embed_utterance's tail (model.py:185-186) for S speakers at once: speaker s = rows [offsets[s], offsets[s+1]) of
+ * embeds; speaker_embeds[s] = mean of those rows, divided by its L2 norm.  offsets: DEVICE int32 [S+1]. */
+int avc_se_reduce(avc_handle h, const float* embeds, const int32_t* offsets, int S, float* speaker_embeds, void* stream);
+
 void avc_destroy(avc_handle h);
 
 /* Last error message of this handle (or of the failed avc_create when h == NULL). Never NULL. */
 const char* avc_last_error(avc_handle h);
 
 /* ABI version; bumped on any signature change. */
-int avc_abi_version(void);
+int avc_abi_version(void);   /* 2: speaker-encoder entry points */
 
 #ifdef __cplusplus
 }

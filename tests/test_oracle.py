@@ -92,17 +92,8 @@ def test_batch_forward_overlap_average_golden():
 
 def test_speaker_encoder_golden():
     g = load_golden("speaker_encoder_p8")
-    rng = np.random.default_rng(int(g["seed"]))
-    names = []
-    for l in range(3):
-        names += [f"lstm.weight_ih_l{l}", f"lstm.weight_hh_l{l}", f"lstm.bias_ih_l{l}", f"lstm.bias_hh_l{l}"]
-    names += ["linear.weight", "linear.bias"]
-    shapes = {"lstm.weight_ih_l0": (1024, 40), "linear.weight": (256, 256), "linear.bias": (256,)}
-    sd = {}
-    for n in names:
-        shp = shapes.get(n, (1024, 256) if "weight" in n else (1024,))
-        sd[n] = torch.from_numpy(rng.uniform(-1 / 16, 1 / 16, size=shp).astype(np.float32))
-    parts = torch.from_numpy(rng.normal(size=(8, 160, 40)).astype(np.float32))
+    from autovc_b200.synth import synth_speaker_encoder
+    sd, parts = synth_speaker_encoder(int(g["seed"]))
     emb = O.speaker_encoder_forward(sd, parts)
     assert float((emb - torch.from_numpy(g["partial_embeds"])).abs().max()) <= FP32_TOL
     utt = O.embed_utterance_from_partials(sd, parts)
