@@ -528,10 +528,12 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = plan->grids[i]; cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = (size_t)plan->smem_bytes; cfg.stream = s;
         cudaLaunchAttribute at[2];
-        at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
-        at[1].id = cudaLaunchAttributeClusterDimension;      // CTA pairs: adjacent unit slices of one batch tile
-        at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
-        cfg.attrs = at; cfg.numAttrs = 2;
+        at[0].id = cudaLaunchAttributeClusterDimension;      // CTA pairs: adjacent unit slices of one batch tile
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
+        // AVC_LSTM_NOCOOP: profiling aid (ncu refuses cooperative cluster launches); the grid is sized to be
+        // co-resident either way, the attribute only makes the driver check it
+        cfg.attrs = at; cfg.numAttrs = getenv("AVC_LSTM_NOCOOP") ? 1 : 2;
         e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb), kargs);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;

@@ -38,7 +38,12 @@ struct TcGemmArgs {
     void* out; int out_type; int ldo;
     float* out_t; const float* res_t;
     uint32_t idesc;
+    int tma_out;                         // row-major output leaves through shared memory + TMA stores (tmO)
+    int ob_t, ob_b;                      // frames x utterances of one epilogue warp's 32 tile rows
 };
+
+constexpr int OUT_STAGE_BYTES = 32 * 128;         // one epilogue warp's 32 rows x 128 bytes, SWIZZLE_128B
+constexpr int OUT_STAGING_BYTES = 4 * 2 * OUT_STAGE_BYTES;   // 4 epilogue warps, double-buffered
 
 template <int BLOCK_N>
 struct Cfg {
@@ -47,7 +52,7 @@ struct Cfg {
     static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
     static constexpr int ACC_STRIDE = BLOCK_N <= 128 ? 128 : 256;   // TMEM columns per accumulator stage
     static constexpr uint32_t TMEM_COLS = 2 * ACC_STRIDE;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_STAGING_BYTES + 1024 /*align*/ + 256 /*barriers*/;
     static_assert(W_STAGE_BYTES % 1024 == 0, "stage buffers must stay 1024-byte aligned for SWIZZLE_128B");
 };
 
@@ -60,13 +65,15 @@ __device__ __forceinline__ float fast_tanh(float x) {
 
 template <int BLOCK_N>
 __global__ void __launch_bounds__(192, 1)
-tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const TcGemmArgs a) {
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmO,
+               const TcGemmArgs a) {
     using C = Cfg<BLOCK_N>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = smem;
     uint8_t* sW = smem + C::STAGES * A_STAGE_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint8_t* sOut = smem + C::STAGES * C::STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sOut + OUT_STAGING_BYTES);
     uint64_t* full = bars;
     uint64_t* empty = bars + C::STAGES;
     uint64_t* tfull = bars + 2 * C::STAGES;
@@ -79,6 +86,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmW);
+        if (a.tma_out) ptx::prefetch_tmap(&tmO);
         for (int i = 0; i < C::STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tfull[i], 1); ptx::mbar_init(&tempty[i], 128); }
         ptx::fence_barrier_init();
@@ -150,6 +158,74 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             ptx::mbar_wait(&tfull[as], aphase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE);
+            if (a.tma_out) {
+                // Row-major output: each warp stages 32 rows x 128 bytes (XOR-swizzled 16-byte pieces: conflict-free for the
+                // row-per-lane writes) and one lane hands the box to TMA - full-line global writes instead of 32 rows x 16 B
+                // per store instruction.  Two staging buffers per warp; rows beyond the tensor are clipped by the TMA unit.
+                const int cw = a.out_type == DT_F32 ? 32 : 64;               // columns per 128-byte staging row
+                const int r0 = q * 32;
+                const int ct = (mt % a.tiles_t) * a.TB + r0 % a.TB, cb = (mt / a.tiles_t) * a.BB + r0 / a.TB;
+                uint8_t* stg = sOut + q * 2 * OUT_STAGE_BYTES;
+                const uint32_t my_row = ptx::smem_u32(stg) + (uint32_t)(lane * 128);
+#pragma unroll 1
+                for (int c0 = 0; c0 < BLOCK_N; c0 += cw) {
+                    const uint32_t buf = (uint32_t)((c0 / cw) & 1) * OUT_STAGE_BYTES;
+                    if (lane == 0) ptx::bulk_wait_group_read<1>();           // the store that last read this buffer is done
+                    __syncwarp();
+#pragma unroll 1
+                    for (int sub = 0; sub < cw; sub += 16) {
+                        uint32_t rr[16];
+                        ptx::tmem_ld16(taddr + (uint32_t)(c0 + sub), rr);
+                        ptx::tmem_ld_wait();
+                        float v[16];
+                        const int n = n0 + c0 + sub;
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4) {
+                            const float4 bv = a.bias ? __ldg(reinterpret_cast<const float4*>(a.bias + n + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            v[j + 0] = __uint_as_float(rr[j + 0]) + bv.x;
+                            v[j + 1] = __uint_as_float(rr[j + 1]) + bv.y;
+                            v[j + 2] = __uint_as_float(rr[j + 2]) + bv.z;
+                            v[j + 3] = __uint_as_float(rr[j + 3]) + bv.w;
+                        }
+                        if (a.act == ACT_RELU) {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.0f);
+                        } else if (a.act == ACT_TANH) {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) v[j] = fast_tanh(v[j]);
+                        }
+                        if (a.out_type == DT_F32) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const uint32_t piece = (uint32_t)(sub / 4 + j);
+                                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + buf + ((piece ^ (uint32_t)(lane & 7)) << 4)),
+                                             "f"(v[4 * j]), "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+                            }
+                        } else {
+                            uint32_t pk[8];
+                            if (a.out_type == DT_BF16) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) { __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]); pk[j] = *reinterpret_cast<uint32_t*>(&h2); }
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) { __half2 h2 = __floats2half2_rn(v[2 * j], v[2 * j + 1]); pk[j] = *reinterpret_cast<uint32_t*>(&h2); }
+                            }
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) {
+                                const uint32_t piece = (uint32_t)(sub / 8 + j);
+                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + buf + ((piece ^ (uint32_t)(lane & 7)) << 4)),
+                                             "r"(pk[4 * j]), "r"(pk[4 * j + 1]), "r"(pk[4 * j + 2]), "r"(pk[4 * j + 3]) : "memory");
+                            }
+                        }
+                    }
+                    ptx::fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        ptx::tma_store_3d(&tmO, stg + buf, n0 + c0, ct, cb);
+                        ptx::bulk_commit_group();
+                    }
+                }
+            } else
 #pragma unroll 1
             for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
                 uint32_t rr[16];
@@ -207,6 +283,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
     }
 
+    if (a.tma_out && warp >= 2 && lane == 0) ptx::bulk_wait_group<0>();   // staged output has left shared memory
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -223,7 +300,7 @@ EncodeTiledFn g_encode = nullptr;
 }  // namespace
 
 struct TcGemmPlan {
-    CUtensorMap tmA, tmW;
+    CUtensorMap tmA, tmW, tmO;
     TcGemmArgs args;
     int block_n;
     int grid;
@@ -309,6 +386,24 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(W) failed: %d", (int)r); return bad(msg); }
     }
+    // ---- row-major output through TMA stores: one box = an epilogue warp's 32 tile rows x 128 bytes ----
+    a.tma_out = 0;
+    plan->tmO = plan->tmW;
+    const int cw = p.out_type == DT_F32 ? 32 : 64;
+    if (p.out && bn % cw == 0 && !getenv("AVC_GEMM_NO_TMA_STORE") && ((uintptr_t)p.out % 16) == 0) {
+        a.ob_t = a.TB >= 32 ? 32 : a.TB; a.ob_b = 32 / a.ob_t;
+        const size_t es = dtype_size(p.out_type);
+        const CUtensorMapDataType odt = p.out_type == DT_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                      : p.out_type == DT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+        cuuint64_t gdim[3] = {(cuuint64_t)p.N, (cuuint64_t)a.gT, (cuuint64_t)a.gB};
+        cuuint64_t gstr[2] = {(cuuint64_t)p.ldo * es, (cuuint64_t)a.gT * p.ldo * es};
+        cuuint32_t box[3] = {(cuuint32_t)cw, (cuuint32_t)a.ob_t, (cuuint32_t)a.ob_b};
+        cuuint32_t est[3] = {1, 1, 1};
+        CUresult r = g_encode(&plan->tmO, odt, 3, p.out, gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(out) failed: %d", (int)r); return bad(msg); }
+        a.tma_out = 1;
+    }
     return plan;
 }
 
@@ -320,9 +415,9 @@ cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t,
     args.out_t = out_t;
     args.res_t = res_t;
     switch (plan->block_n) {
-        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, args); break;
-        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, args); break;
-        default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, args); break;
+        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, args); break;
+        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, args); break;
+        default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, args); break;
     }
     return cudaGetLastError();
 }
