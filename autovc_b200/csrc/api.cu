@@ -73,6 +73,7 @@ struct avc_ctx {
     int precision = AVC_PREC_BF16;
     int num_sms = 148;
     bool loaded = false;
+    bool gx_f32 = false;       // AVC_GX_F32: keep lstm2's gate pre-activations in fp32 (A/B aid)
     bool se_loaded = false;    // avc_se_load_weights completed
     bool force_simt = false;   // AVC_FORCE_SIMT=1: debugging aid, run the GEMMs of the bf16 mode on the CUDA cores
     std::string err = "";
@@ -313,16 +314,24 @@ struct Runner {
 
     // Full-sequence LSTM layer from a hoisted input projection Gx.
     //   Gx: [B][Tg][ndir*4H] fp32 (row for frame t is t/gx_div);  Y: [B][T][ndir*H] of h_type.
-    void lstm(int lid_hh, const float* Gx, int Tg, int gx_div, void* Y, int h_type, int H, int ndir) {
+    // true when lstm() takes the in-band-exchange tensor-core kernel for this layer (which also accepts fp16 Gx)
+    bool ll_path(int lid_hh, int h_type, int H, int ndir) const {
+        return use_tc() && !h->simt_lstm && !h->old_lstm && ndir == 1 && h_type == DT_BF16 && h->layers[lid_hh].w_type == DT_BF16 && H % 256 == 0 && H <= 1024;
+    }
+    // fp16 gate pre-activations for the big recurrent layers: halves the Gx write + read (1 GB per forward at config 2)
+    int gx_type(int lid_hh, int h_type, int H) const { return ll_path(lid_hh, h_type, H, 1) && !h->gx_f32 ? DT_F16 : DT_F32; }
+
+    void lstm(int lid_hh, const void* Gx_, int gx_t, int Tg, int gx_div, void* Y, int h_type, int H, int ndir) {
+        const float* Gx = (const float*)Gx_;
         if (!ok()) return;
         const Layer& L = h->layers[lid_hh];
         mark(lid_hh <= L_ENC_L1_HH ? AVC_PHASE_ENC_LSTM : (lid_hh == L_DEC_LSTM1_HH ? AVC_PHASE_LSTM1 : AVC_PHASE_LSTM2));
         const size_t hs = dtype_size(h_type);
-        if (use_tc() && !h->simt_lstm && !h->old_lstm && ndir == 1 && h_type == DT_BF16 && L.w_type == DT_BF16 && H % 256 == 0) {
+        if (ll_path(lid_hh, h_type, H, ndir)) {
             // persistent tensor-core recurrence, in-band validity exchange (ll_lstm.cu)
             if (building_plans) {
                 const char* why = nullptr;
-                LlLstmPlan* plan = ll_lstm_plan_create(L.w_dev, Gx, Tg, gx_div, Y, wsp->Yb, B, T, H, h->num_sms, &why);
+                LlLstmPlan* plan = ll_lstm_plan_create(L.w_dev, Gx_, gx_t, Tg, gx_div, Y, wsp->Yb, B, T, H, h->num_sms, &why);
                 if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core LSTM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
                 h->llplans.push_back(plan);
             }
@@ -331,6 +340,7 @@ struct Runner {
             h->launches += n;
             return;
         }
+        if (gx_t != DT_F32) { rc = fail(h, AVC_ERR_UNSUPPORTED, "fp16 Gx outside the ll_lstm path"); return; }
         if (use_tc() && !h->simt_lstm && ndir == 1 && h_type == DT_BF16 && L.w_type == DT_BF16 && H % 64 == 0) {
             // persistent tensor-core recurrence (tc_lstm.cu)
             if (building_plans) {
@@ -425,9 +435,9 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
                                    B, T, d.freq, r.s, &n), "enc lstm l1");
         h->launches += n;
     } else {
-        r.lstm(L_ENC_L0_HH, w.GxE, T, 1, w.Y0, at, dn, 2);
+        r.lstm(L_ENC_L0_HH, w.GxE, DT_F32, T, 1, w.Y0, at, dn, 2);
         r.gemm(L_ENC_L1_IH, w.Y0, at, 2 * dn, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
-        r.lstm(L_ENC_L1_HH, w.GxE, T, 1, w.Y1, DT_F32, dn, 2);
+        r.lstm(L_ENC_L1_HH, w.GxE, DT_F32, T, 1, w.Y1, DT_F32, dn, 2);
         // code sampling + de-duplicated decoder input (encoder.py:94-95, model.py:99-124)
         r.mark(AVC_PHASE_LAYOUT);
         r.check(launch_codes(w.Y1, c_trg, codes, encode_only ? nullptr : w.Dm, at, B, T, dn, E, d.freq, r.s), "codes"); h->launches++;
@@ -436,14 +446,15 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     if (!encode_only) {
         // ---- decoder (reference decoder.py:58-79) ----
         r.gemm(L_DEC_LSTM1_IH, w.Dm, at, 2 * dn + E, B * nb, nb, ACT_NONE, w.Gd1, DT_F32, 4 * P);
-        r.lstm(L_DEC_LSTM1_HH, w.Gd1, nb, d.freq, w.H1, at, P, 1);
+        r.lstm(L_DEC_LSTM1_HH, w.Gd1, DT_F32, nb, d.freq, w.H1, at, P, 1);
         r.gemm(L_DEC_CONV0, w.H1, at, P, M, T, ACT_RELU, w.actA, at, P);
         r.gemm(L_DEC_CONV1, w.actA, at, P, M, T, ACT_RELU, w.actB, at, P);
         r.gemm(L_DEC_CONV2, w.actB, at, P, M, T, ACT_RELU, w.actA, at, P);
-        r.gemm(L_DEC_L2_0_IH, w.actA, at, P, M, T, ACT_NONE, w.G2, DT_F32, 4 * LSTM2_H);
-        r.lstm(L_DEC_L2_0_HH, w.G2, T, 1, w.H2a, at, LSTM2_H, 1);
-        r.gemm(L_DEC_L2_1_IH, w.H2a, at, LSTM2_H, M, T, ACT_NONE, w.G2, DT_F32, 4 * LSTM2_H);
-        r.lstm(L_DEC_L2_1_HH, w.G2, T, 1, w.H2b, at, LSTM2_H, 1);
+        const int g2t = r.gx_type(L_DEC_L2_0_HH, at, LSTM2_H);
+        r.gemm(L_DEC_L2_0_IH, w.actA, at, P, M, T, ACT_NONE, w.G2, g2t, 4 * LSTM2_H);
+        r.lstm(L_DEC_L2_0_HH, w.G2, g2t, T, 1, w.H2a, at, LSTM2_H, 1);
+        r.gemm(L_DEC_L2_1_IH, w.H2a, at, LSTM2_H, M, T, ACT_NONE, w.G2, g2t, 4 * LSTM2_H);
+        r.lstm(L_DEC_L2_1_HH, w.G2, g2t, T, 1, w.H2b, at, LSTM2_H, 1);
         // linear projection -> mel (B,80,T) fp32 + channel-last copy for the postnet (decoder.py:77, model.py:127)
         r.gemm(L_DEC_LINEAR, w.H2b, at, LSTM2_H, M, T, ACT_NONE, w.melc, pt, N_MELS, mel, nullptr);
         // ---- postnet + residual (reference postnet.py:50-63, model.py:131-132) ----
@@ -527,7 +538,7 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
     char* bufs[2] = {w.Ya, w.Yb2};
     for (int l = 0; l < SE_LAYERS; ++l) {
         r.gemm(L_SE_L0_IH + 2 * l, in, at, ldin, M, T, ACT_NONE, w.Gx, DT_F32, 4 * SE_H);
-        r.lstm(L_SE_L0_HH + 2 * l, w.Gx, T, 1, bufs[l & 1], at, SE_H, 1);
+        r.lstm(L_SE_L0_HH + 2 * l, w.Gx, DT_F32, T, 1, bufs[l & 1], at, SE_H, 1);
         in = bufs[l & 1]; ldin = SE_H;
     }
     // hidden[-1] = last layer's h at the final frame (model.py:83-85): rows of pitch T*H starting at frame T-1
@@ -574,6 +585,7 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
     h->simt_lstm = sl && sl[0] == '1';
     const char* li = getenv("AVC_LSTM_IMPL");
     h->old_lstm = li && li[0] == 't';
+    h->gx_f32 = getenv("AVC_GX_F32") != nullptr;
     for (int i = 0; i < L_COUNT; ++i) h->layers[i].name = kLayerNames[i];
     if (device >= 0) {
         cudaError_t e = cudaSetDevice(device);

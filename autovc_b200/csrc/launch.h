@@ -41,7 +41,7 @@ cudaError_t launch_tc_lstm(const TcLstmPlan* plan, cudaStream_t s, int* launches
 struct LlLstmPlan;
 const char* ll_lstm_init();
 size_t ll_lstm_exchange_bytes(int B, int T, int H);
-LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, void* Yx, int B, int T, int H,
+LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_type, int Tg, int gx_div, void* Y, void* Yx, int B, int T, int H,
                                 int num_sms, const char** err);
 void ll_lstm_plan_destroy(LlLstmPlan* plan);
 cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches);

@@ -73,7 +73,7 @@ constexpr int MAX_KB = 16;
 struct LlLstmArgs {
     int B, T, H;
     int gx_div;                  // Gx row for frame t is t / gx_div (lstm1 reads the de-duplicated projection)
-    const float* Gx;             // [B][Tg][4H] fp32, unit-major gate order, bias included
+    const void* Gx;              // [B][Tg][4H] fp32 (or fp16: GXH kernels), unit-major gate order, bias included
     const __nv_bfloat16* Whh;    // [4H][H] bf16, unit-major gate rows
     __nv_bfloat16* Y;            // [B][T][H] bf16 output sequence for the next layer
     __nv_bfloat16* Yx;           // exchange copy: [T][tiles][H/8][64][8] bf16, pre-filled with 0xFF
@@ -124,7 +124,7 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
-template <int NKB>
+template <int NKB, bool GXH>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     constexpr int NKB_T = NKB < MAX_TMEM_CHUNKS ? NKB : MAX_TMEM_CHUNKS;   // W chunks resident in tensor memory
@@ -221,17 +221,38 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         for (int k = 0; k < 8; ++k) c[k] = 0.0f;
         const uint32_t gx_smem = ptx::smem_u32(sGx);
         const uint32_t ht_smem = ptx::smem_u32(sHT);
-        // Gx staging: thread e copies pieces e + 256 i (i < 8): utterance = id / 32, 16-byte segment = id % 32
+        // Gx staging: thread e copies 16-byte pieces e + 256 i of the tile's [utterance][gate row] block
         auto stage_gx = [&](int t) {
             const size_t toff = (size_t)(t / a.gx_div) * a.gx_st + (size_t)ns * MROWS;
+            if constexpr (GXH) {      // fp16: 256 bytes per utterance
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int id = threadIdx.x + EPI_THREADS * i;
-                const int u = id >> 5, seg = id & 31;
-                const int b = b0 + u < a.B ? b0 + u : a.B - 1;
-                cp_async16(gx_smem + (uint32_t)(u * (MROWS * 4) + seg * 16), a.Gx + (size_t)b * a.gx_sb + toff + seg * 4);
+                for (int i = 0; i < 4; ++i) {
+                    const int id = threadIdx.x + EPI_THREADS * i;
+                    const int u = id >> 4, seg = id & 15;
+                    const int b = b0 + u < a.B ? b0 + u : a.B - 1;
+                    cp_async16(gx_smem + (uint32_t)(u * (MROWS * 2) + seg * 16),
+                               reinterpret_cast<const __half*>(a.Gx) + (size_t)b * a.gx_sb + toff + seg * 8);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int id = threadIdx.x + EPI_THREADS * i;
+                    const int u = id >> 5, seg = id & 31;
+                    const int b = b0 + u < a.B ? b0 + u : a.B - 1;
+                    cp_async16(gx_smem + (uint32_t)(u * (MROWS * 4) + seg * 16),
+                               reinterpret_cast<const float*>(a.Gx) + (size_t)b * a.gx_sb + toff + seg * 4);
+                }
             }
             cp_async_commit();
+        };
+        auto gx_at = [&](int k) -> float {      // Gx_t[utterance half*32 + k][gate row R]
+            if constexpr (GXH) {
+                uint16_t hbits;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hbits) : "r"(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 2)));
+                return __half2float(__ushort_as_half(hbits));
+            } else {
+                return ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
+            }
         };
         // output geometry of the final 16-byte stores: thread e -> utterance e/4, 8-unit piece e%4
         const int ou = threadIdx.x >> 2, op = threadIdx.x & 3;
@@ -344,7 +365,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 const float ps = gj == 2 ? 1.0f : 0.5f, po = gj == 2 ? 0.0f : 0.5f;
 #pragma unroll
                 for (int k = 0; k < 32; ++k) {
-                    const float x = act[k] + ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
+                    const float x = act[k] + gx_at(k);
                     float th;
                     asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(ps * x));
                     act[k] = fmaf(ps, th, po);
@@ -352,7 +373,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             } else {
 #pragma unroll
                 for (int k = 0; k < 32; ++k) {
-                    const float x = act[k] + ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
+                    const float x = act[k] + gx_at(k);
                     act[k] = __fdividef(act_s, 1.0f + __expf(-act_s * x)) + act_o;
                 }
             }
@@ -429,11 +450,11 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode_ll = nullptr;
 
-const void* kernel_for(int nkb) {
+const void* kernel_for(int nkb, bool gxh) {
     switch (nkb) {
-        case 16: return (const void*)ll_lstm_kernel<16>;
-        case 8: return (const void*)ll_lstm_kernel<8>;
-        default: return (const void*)ll_lstm_kernel<4>;
+        case 16: return gxh ? (const void*)ll_lstm_kernel<16, true> : (const void*)ll_lstm_kernel<16, false>;
+        case 8: return gxh ? (const void*)ll_lstm_kernel<8, true> : (const void*)ll_lstm_kernel<8, false>;
+        default: return gxh ? (const void*)ll_lstm_kernel<4, true> : (const void*)ll_lstm_kernel<4, false>;
     }
 }
 
@@ -449,6 +470,7 @@ struct LlLstmPlan {
     std::vector<LlLstmArgs> args;
     std::vector<dim3> grids;
     int nkb;
+    bool gx_f16;
     int smem_bytes;
     void* yx_base; size_t yx_bytes;       // region to pre-fill with the "unwritten" pattern before every launch
 };
@@ -459,8 +481,8 @@ const char* ll_lstm_init() {
     cudaDriverEntryPointQueryResult qres;
     cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
     if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return "cuTensorMapEncodeTiled not available from the driver";
-    for (int nkb : {16, 8, 4})
-        if (cudaFuncSetAttribute(kernel_for(nkb), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_for(nkb)) != cudaSuccess)
+    for (int i = 0; i < 6; ++i)
+        if (cudaFuncSetAttribute(kernel_for(4 << (i >> 1), i & 1), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_for(4 << (i >> 1))) != cudaSuccess)
             return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed for ll_lstm_kernel";
     g_encode_ll = reinterpret_cast<EncodeTiledFn>(fn);
     return nullptr;
@@ -468,17 +490,19 @@ const char* ll_lstm_init() {
 
 size_t ll_lstm_exchange_bytes(int B, int T, int H) { return (size_t)T * ceil_div(B, TILE_N) * TILE_N * H * 2; }
 
-LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, void* Yx, int B, int T, int H,
+LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_type, int Tg, int gx_div, void* Y, void* Yx, int B, int T, int H,
                                 int num_sms, const char** err) {
     static thread_local char msg[256];
     auto bad = [&](const char* m) -> LlLstmPlan* { if (err) *err = m; return nullptr; };
     if (!g_encode_ll) return bad("ll_lstm_init() not called");
     if (H != 1024 && H != 512 && H != 256) return bad("hidden size must be 256, 512 or 1024");
+    if (gx_type != DT_F32 && gx_type != DT_F16) return bad("Gx must be fp32 or fp16");
     const int G_n = H / SLICE_UNITS, nkb = H / KBLK;
     if (G_n > num_sms) return bad("hidden size too large for one co-resident grid");
     LlLstmPlan* plan = new LlLstmPlan();
     plan->nkb = nkb;
     plan->smem_bytes = smem_for(nkb);
+    plan->gx_f16 = gx_type == DT_F16;
     plan->yx_base = Yx; plan->yx_bytes = ll_lstm_exchange_bytes(B, T, H);
     {
         cuuint64_t gdim[2] = {(cuuint64_t)H, (cuuint64_t)4 * H};
@@ -497,7 +521,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, i
         LlLstmArgs a{};
         a.B = Bc; a.T = T; a.H = H; a.gx_div = gx_div;
         a.y_sb = (long long)T * H; a.y_st = H; a.gx_sb = (long long)Tg * 4 * H; a.gx_st = 4LL * H;
-        a.Gx = Gx + (size_t)bs * a.gx_sb;
+        a.Gx = (const char*)Gx + (size_t)bs * a.gx_sb * dtype_size(gx_type);
         a.Whh = reinterpret_cast<const __nv_bfloat16*>(Whh_bf16);
         a.Y = reinterpret_cast<__nv_bfloat16*>(Y) + (size_t)bs * a.y_sb;
         a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
@@ -534,7 +558,7 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
         // AVC_LSTM_NOCOOP: profiling aid (ncu refuses cooperative cluster launches); the grid is sized to be
         // co-resident either way, the attribute only makes the driver check it
         cfg.attrs = at; cfg.numAttrs = getenv("AVC_LSTM_NOCOOP") ? 1 : 2;
-        e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb), kargs);
+        e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb, plan->gx_f16), kargs);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
         if (tracing) {   // debugging aid: synchronous dump of the per-step timeline of CTA (0,0)
