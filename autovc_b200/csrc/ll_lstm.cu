@@ -292,6 +292,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                             __trap();
                         }
                     }
+                    if (i == NP - 1 && threadIdx.x == 0) AVC_TRACE(9);
                     const int row = piece_row(i), pl = piece_plane(i);
                     st_shared_v4(sH_chunk + (uint32_t)(row * 128 + ((pl ^ (row & 7)) << 4)), v[i]);
                 }
@@ -311,6 +312,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                         ptx::mbar_wait(&gfull[g], (uint32_t)(t - 1) & 1);
                         ptx::tc_fence_after();
                         if (g == 0) AVC_TRACE(2);
+                        AVC_TRACE(10 + g);
 #pragma unroll
                         for (int cc = 0; cc < NKB / 4; ++cc) {
                             const int c = g * (NKB / 4) + cc;
@@ -330,7 +332,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                         }
                     }
                     ptx::umma2_commit_warp(acc_full);       // -> acc_full of BOTH CTAs
-                    if (ih == 1) AVC_TRACE(3);
+                    if (ih == 1) AVC_TRACE(3); else AVC_TRACE(14);
                 }
                 if (threadIdx.x == 0) AVC_TRACE(1);
             }
@@ -574,6 +576,7 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
                 fprintf(stderr, "  t=%d:", TRACE_T0 + st);
                 for (int p = 1; p <= 5; ++p) fprintf(stderr, " %6lld", r[p] - r[0]);
                 fprintf(stderr, " (%lld %lld %lld)", r[6] - r[0], r[7] - r[0], r[8] - r[0]);
+                fprintf(stderr, " [landed %lld groups %lld %lld %lld %lld issued0 %lld]", r[9] - r[0], r[10] - r[0], r[11] - r[0], r[12] - r[0], r[13] - r[0], r[14] - r[0]);
                 if (st + 1 < TRACE_STEPS && r[TRACE_PTS]) fprintf(stderr, " | %6lld", r[TRACE_PTS] - r[0]);
                 fprintf(stderr, "\n");
             }
