@@ -87,27 +87,26 @@ __global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
     const size_t gx_pitch = (size_t)a.T * 8 * EH;            // floats per utterance
     const float* gx = a.Gx + (size_t)(ok ? b : 0) * gx_pitch + dir * 4 * EH + q * 32;
 
-    // software pipeline: the hoisted input projection of step+1 is in flight while step is computed
-    float4 x_next[8];
-    {
-        const int t0 = dir == 0 ? 0 : a.T - 1;
-        const float4* p = reinterpret_cast<const float4*>(gx + (size_t)t0 * 8 * EH);
+    // software pipeline: the hoisted input projections of the next NST-1 steps are in flight (cp.async into a private
+    // shared-memory ring, [stage][w][lane] so that the 16-byte reads are conflict-free) while a step is computed: an L2 hit
+    // costs 1.1-1.3k cycles on this part, about one step of this kernel
+    constexpr int NST = 8;
+    __shared__ float4 ring[NST][8][32];
+    auto prefetch = [&](int step) {
+        if (step < a.T) {
+            const int tt = dir == 0 ? step : a.T - 1 - step;
+            const float* p = gx + (size_t)tt * 8 * EH;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) x_next[w] = __ldg(p + w);
-    }
-
-    for (int step = 0; step < a.T; ++step) {
-        const int t = dir == 0 ? step : a.T - 1 - step;
-        float4 x[8];
-#pragma unroll
-        for (int w = 0; w < 8; ++w) x[w] = x_next[w];
-        if (step + 1 < a.T) {
-            const int tn = dir == 0 ? t + 1 : t - 1;
-            const float4* p = reinterpret_cast<const float4*>(gx + (size_t)tn * 8 * EH);
-#pragma unroll
-            for (int w = 0; w < 8; ++w) x_next[w] = __ldg(p + w);
+            for (int w = 0; w < 8; ++w)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(&ring[step % NST][w][lane])), "l"(p + 4 * w) : "memory");
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");      // one group per step, empty past the end
+    };
+#pragma unroll
+    for (int i = 0; i < NST - 1; ++i) prefetch(i);
 
+    auto do_step = [&](int step, const float4 (&x)[8]) {
+        const int t = dir == 0 ? step : a.T - 1 - step;
         float h[8];
 #pragma unroll
         for (int w = 0; w < 8; ++w) {
@@ -149,6 +148,15 @@ __global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
                 if (dir == 0 && j == nf - 1 && nb > nf) *reinterpret_cast<uint4*>(dp + a.ldd) = v;
             }
         }
+    };
+
+    for (int step = 0; step < a.T; ++step) {
+        prefetch(step + NST - 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(NST - 1) : "memory");   // this thread's pieces of `step` have landed
+        float4 x[8];
+#pragma unroll
+        for (int w = 0; w < 8; ++w) x[w] = ring[step % NST][w][lane];
+        do_step(step, x);
     }
 }
 
