@@ -273,6 +273,14 @@ def main():
         dom_flops = 2.0 * MAC_PER_FRAME[dom] * B * T
         achieved = dom_flops / (phase_ms[dom] * 1e-3) / 1e12 if phase_ms[dom] > 0 else 0.0
         peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+        # DRAM bytes of the dominant phase's launches from the committed ncu --set full capture (same config), or null
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_ncu_traffic.json")))
+            if (B, T) == (256, 128) and args.precision == "bf16":
+                traffic = tj["bytes_per_step"].get(dom)
+        except Exception:
+            traffic = None
         line = {
             "metric": "generator_fwd_mel_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak",
@@ -289,7 +297,7 @@ def main():
             "clocks": clocks,
             "phase_ms": {k: round(v, 4) for k, v in phase_ms.items()},
             "roofline": {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": f"{peak_src} bf16_tflops_sustained",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": f"{peak_src} bf16_tflops_sustained",
                          "algorithmic_flop_per_launch_group": dom_flops},
             "wall_s_timed_region": wall,
         }
