@@ -22,11 +22,18 @@ AVC_PREC_FP32 = 1
 
 EXPORTS = ["avc_abi_version", "avc_create", "avc_load_weights", "avc_workspace_bytes", "avc_forward", "avc_encode",
            "avc_last_launch_count", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error",
-           "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_reduce"]
+           "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_reduce",
+           "avc_mel_create", "avc_mel_num_frames", "avc_mel_filterbank", "avc_mel_forward", "avc_mel_last_error", "avc_mel_destroy"]
 
 
 class AvcDims(Structure):
     _fields_ = [("dim_neck", c_int32), ("dim_emb", c_int32), ("dim_pre", c_int32), ("freq", c_int32)]
+
+
+class AvcMelConfig(Structure):
+    _fields_ = [("sr", c_int32), ("n_fft", c_int32), ("hop_length", c_int32), ("win_length", c_int32), ("n_mels", c_int32),
+                ("fmin", c_float), ("fmax", c_float), ("power", c_int32), ("log_normalize", c_int32), ("min_level_db", c_float),
+                ("pad_reflect", c_int32), ("frames_major", c_int32)]
 
 
 class AvcWeightDesc(Structure):
@@ -76,6 +83,18 @@ def lib() -> ctypes.CDLL:
     L.avc_se_forward.restype = c_int
     L.avc_se_reduce.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]
     L.avc_se_reduce.restype = c_int
+    L.avc_mel_create.argtypes = [POINTER(c_void_p), POINTER(AvcMelConfig), c_int]
+    L.avc_mel_create.restype = c_int
+    L.avc_mel_num_frames.argtypes = [c_void_p, c_int64]
+    L.avc_mel_num_frames.restype = c_int64
+    L.avc_mel_filterbank.argtypes = [c_void_p, POINTER(c_float), c_int64]
+    L.avc_mel_filterbank.restype = c_int64
+    L.avc_mel_forward.argtypes = [c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p]
+    L.avc_mel_forward.restype = c_int
+    L.avc_mel_last_error.argtypes = [c_void_p]
+    L.avc_mel_last_error.restype = c_char_p
+    L.avc_mel_destroy.argtypes = [c_void_p]
+    L.avc_mel_destroy.restype = None
     L.avc_destroy.argtypes = [c_void_p]
     L.avc_destroy.restype = None
     L.avc_last_error.argtypes = [c_void_p]

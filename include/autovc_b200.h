@@ -147,11 +147,50 @@ int avc_se_reduce(avc_handle h, const float* embeds, const int32_t* offsets, int
 
 void avc_destroy(avc_handle h);
 
+/* ---- mel front-end: wav -> mel spectrogram on the device -------------------------------------
+ * Replaces mel_spec_auto_encoder / mel_spec_speaker_encoder (reference autovc/audio/spectrogram.py:62-142, 144-217), i.e.
+ * librosa.stft + librosa.filters.mel + amp_to_db + normalize_spec, for one parameter set per handle.  Independent of
+ * avc_handle: a front-end owns only its window, twiddle and filterbank tables. */
+typedef struct avc_mel_ctx* avc_mel_handle;
+
+typedef struct avc_mel_config {
+    int32_t sr;             /* 22050 (generator, hparams.py:7) / 16000 (speaker encoder, :53) */
+    int32_t n_fft;          /* 2048 / 400 = int(sr * 25 ms) (spectrogram.py:199) */
+    int32_t hop_length;     /* 275 / 160 */
+    int32_t win_length;     /* 1100 / 0 = n_fft: periodic Hann, zero-padded to n_fft and centred like librosa */
+    int32_t n_mels;         /* 80 / 40 */
+    float fmin;             /* 40 / 0 */
+    float fmax;             /* <= 0: sr / 2 */
+    int32_t power;          /* 1: |X| (generator: melspectrogram(S=abs(stft))), 2: |X|^2 (speaker encoder) */
+    int32_t log_normalize;  /* 1: clip((20 log10(max(1e-5, mel)) - min_level_db) / -min_level_db, 0, 1) (spectrogram.py:14-32,53-55) */
+    float min_level_db;     /* -100; >= 0 selects -100 */
+    int32_t pad_reflect;    /* 1: librosa <= 0.9 centre padding (reflect); 0: zeros (librosa >= 0.10) */
+    int32_t frames_major;   /* 0: out[n_mels][n_frames] (generator, (80, T)); 1: out[n_frames][n_mels] (speaker encoder, .T at :204) */
+} avc_mel_config;
+
+/* device < 0: host-only handle (filterbank construction and frame arithmetic work, avc_mel_forward fails). */
+int avc_mel_create(avc_mel_handle* out, const avc_mel_config* cfg, int device);
+
+/* librosa's centred framing: 1 + n_samples / hop_length. */
+int64_t avc_mel_num_frames(avc_mel_handle h, int64_t n_samples);
+
+/* Copy the dense (n_mels, 1 + n_fft/2) float32 filterbank (= librosa.filters.mel(..., htk=False, norm="slaney")) into
+ * `out` when capacity allows; returns its element count.  Host memory. */
+int64_t avc_mel_filterbank(avc_mel_handle h, float* out, int64_t capacity);
+
+/* B utterances of n_samples float32 each (DEVICE pointer, utterance b at wav + b * wav_stride) -> out (DEVICE), utterance b
+ * at out + b * n_mels * n_frames in the layout `frames_major` selects.  Enqueued on `stream`. */
+int avc_mel_forward(avc_mel_handle h, const float* wav, int B, int64_t n_samples, int64_t wav_stride, float* out, void* stream);
+
+const char* avc_mel_last_error(avc_mel_handle h);   /* h may be NULL: error of the last failed avc_mel_create on this thread */
+void avc_mel_destroy(avc_mel_handle h);
+
+
 /* Last error message of this handle (or of the failed avc_create when h == NULL). Never NULL. */
 const char* avc_last_error(avc_handle h);
 
 /* ABI version; bumped on any signature change. */
-int avc_abi_version(void);   /* 2: speaker-encoder entry points */
+int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end */
 
 #ifdef __cplusplus
 }
