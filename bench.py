@@ -301,7 +301,7 @@ def main():
                          "algorithmic_flop_per_launch_group": dom_flops},
             "wall_s_timed_region": wall,
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:     # the CPU leg is an N=1 measurement (rank 0 would share the host with the other ranks)
             fps, ms, cores = time_oracle(args.cpu_sample_batch, T, 3, 1)
             line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
                                     "sample": f"{args.cpu_sample_batch} of the {B} utterances x {T} frames, 3 timed passes of the oracle port (torch CPU fp32)"}
