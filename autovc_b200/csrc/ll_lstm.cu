@@ -83,6 +83,7 @@ struct LlLstmArgs {
     uint32_t idesc;
     int approx;                  // 1 (default): gate activations with MUFU.TANH (tanh.approx.f32, abs err ~5e-4: below the bf16 rounding of h;
                                  // measured end-to-end error unchanged); AVC_LSTM_EXACT=1 selects ex2/rcp based sigmoid/tanh
+    int canary;                  // AVC_LSTM_CANARY: 0 no canary poll, 1 (default) loader-only warps, 2 all warps (the previous protocol)
     long long* trace;            // optional clock64 trace of CTA (0,0) (AVC_LSTM_TRACE=1), nullptr normally
 };
 
@@ -265,8 +266,11 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             if (t >= 1) {
                 // ---- h_{t-1} chunk: L2 -> registers (poll) -> swizzled operand tile in shared memory ----
                 const __nv_bfloat16* src = chunk_base + (size_t)(t - 1) * step_elems;
-                {   // step start: poll one 16-byte canary per lane; whole-chunk polls would compete with the producers' stores.
-                    // (Several staggered polls in flight were measured slower: the data has usually landed when a warp gets here.)
+                // Epilogue warps get here right after storing their own h_{t-1}: the other slices' pieces are then (measured) already
+                // visible, so they fetch the whole step in one wave and re-fetch only what is still missing - a separate poll before
+                // the wave would be a second L2 round trip (~2k cycles under load) per step.  Loader-only warps arrive a whole epilogue
+                // early; a single 16-byte canary per lane keeps them off the fabric until their producers have stored.
+                if (epi ? a.canary >= 2 : a.canary >= 1) {
                     const __nv_bfloat16* p = src + (size_t)piece_plane(0) * PLANE_STRIDE + piece_row(0) * PLANE_ELEMS;
                     uint4 cn = ld_strong(p);
                     for (uint32_t spin = 0; unwritten(cn); ++spin) {
@@ -279,20 +283,26 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 #pragma unroll
                 for (int i = 0; i < NP; ++i)
                     v[i] = ld_strong(src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS);
+                if (epi) stage_gx(t);                  // Gx_t is needed a whole MMA phase from now: issue it behind the h loads
                 // the MMAs of step t-1 still read the tiles until acc_full(t-1): normally long past
                 if (t >= 2 && !epi) ptx::mbar_wait(acc_full, (uint32_t)(t - 2) & 1);
+                for (uint32_t spin = 0;; ++spin) {          // pieces not written yet: fetch all of them again, together
+                    bool missing = false;
+#pragma unroll
+                    for (int i = 0; i < NP; ++i)
+                        if (unwritten(v[i])) {
+                            v[i] = ld_strong(src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS);
+                            missing = true;
+                        }
+                    if (!missing) break;
+                    if (spin > (1u << 22)) {
+                        printf("autovc_b200: lstm h poll timed out (slice %d tile %d t %d chunk %d lane %d)\n", ns, bt, t, kc, lane);
+                        __trap();
+                    }
+                }
+                if (threadIdx.x == 0) AVC_TRACE(9);
 #pragma unroll
                 for (int i = 0; i < NP; ++i) {
-                    const __nv_bfloat16* p = src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS;
-                    uint32_t spin = 0;
-                    while (unwritten(v[i])) {               // not written yet: poll again
-                        v[i] = ld_strong(p);
-                        if (++spin > (1u << 22)) {
-                            printf("autovc_b200: lstm h poll timed out (slice %d tile %d t %d chunk %d piece %d lane %d)\n", ns, bt, t, kc, i, lane);
-                            __trap();
-                        }
-                    }
-                    if (i == NP - 1 && threadIdx.x == 0) AVC_TRACE(9);
                     const int row = piece_row(i), pl = piece_plane(i);
                     st_shared_v4(sH_chunk + (uint32_t)(row * 128 + ((pl ^ (row & 7)) << 4)), v[i]);
                 }
@@ -434,7 +444,6 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 if (ovalid) *reinterpret_cast<uint4*>(y_out + (size_t)t * a.y_st) = hv4;
             }
             if (threadIdx.x == 0) AVC_TRACE(5);
-            if (t + 1 < a.T) stage_gx(t + 1);
         }
     }
 
@@ -529,6 +538,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
         a.tiles = ceil_div(B, TILE_N); a.tile0 = bs / TILE_N;
         a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
+        { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : 1; }
         a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, TILE_N);      // the pair's MMA: M = 256 (128 gate rows per CTA), N = 64
         plan->args.push_back(a);
         plan->grids.push_back(dim3(G_n, ceil_div(Bc, TILE_N)));
