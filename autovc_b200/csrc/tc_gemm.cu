@@ -38,6 +38,8 @@ struct TcGemmArgs {
     void* out; int out_type; int ldo;
     float* out_t; const float* res_t;
     uint32_t idesc;
+    int full_tiles;                      // tiles [0, full_tiles) are BLOCK_N wide; the rest are the last round's tiles split in two halves
+    uint32_t idesc_half;
     int tma_out;                         // row-major output leaves through shared memory + TMA stores (tmO)
     int ob_t, ob_b;                      // frames x utterances of one epilogue warp's 32 tile rows
 };
@@ -63,10 +65,23 @@ __device__ __forceinline__ float fast_tanh(float x) {
     return 1.0f - __fdividef(2.0f, 1.0f + e);
 }
 
+// Static schedule: tile = blockIdx.x + k * gridDim.x.  When the last round would leave more than half of the CTAs idle, its
+// tiles are split into two half-width tiles each (full_tiles is a multiple of the grid), e.g. 512 tiles on 148 CTAs:
+// 3 full rounds + 68 tiles -> 3 rounds + 136 half tiles = 3.5 instead of 4 rounds.
+template <int BLOCK_N>
+__device__ __forceinline__ void decode_tile(const TcGemmArgs& a, int tile, int& mt, int& n0, int& bn) {
+    if (tile < a.full_tiles) {
+        mt = tile / a.tiles_n; n0 = (tile % a.tiles_n) * BLOCK_N; bn = BLOCK_N;
+    } else {
+        const int h = tile - a.full_tiles, f = a.full_tiles + (h >> 1);
+        mt = f / a.tiles_n; n0 = (f % a.tiles_n) * BLOCK_N + (h & 1) * (BLOCK_N / 2); bn = BLOCK_N / 2;
+    }
+}
+
 template <int BLOCK_N>
 __global__ void __launch_bounds__(192, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmO,
-               const TcGemmArgs a) {
+               const __grid_constant__ CUtensorMap tmWh, const TcGemmArgs a) {
     using C = Cfg<BLOCK_N>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -87,6 +102,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmW);
         if (a.tma_out) ptx::prefetch_tmap(&tmO);
+        if (a.full_tiles < a.num_tiles) ptx::prefetch_tmap(&tmWh);
         for (int i = 0; i < C::STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tfull[i], 1); ptx::mbar_init(&tempty[i], 128); }
         ptx::fence_barrier_init();
@@ -101,15 +117,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // ===================== TMA producer (whole warp, uniform operands, one elected lane issues) =====================
         int stage = 0; uint32_t phase = 0;
         for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-            const int nt = tile % a.tiles_n, mt = tile / a.tiles_n;
+            int mt, n0, bn;
+            decode_tile<BLOCK_N>(a, tile, mt, n0, bn);
             const int t0 = (mt % a.tiles_t) * a.TB, b0 = (mt / a.tiles_t) * a.BB;
-            const int n0 = nt * BLOCK_N;
+            const bool half = bn != BLOCK_N;
             for (int tap = 0; tap < a.taps; ++tap) {
                 for (int kc = 0; kc < a.kblocks_per_tap; ++kc) {
                     ptx::mbar_wait(&empty[stage], phase ^ 1);
-                    ptx::mbar_expect_tx_warp(&full[stage], C::STAGE_BYTES);
+                    ptx::mbar_expect_tx_warp(&full[stage], half ? A_STAGE_BYTES + C::W_STAGE_BYTES / 2 : C::STAGE_BYTES);
                     ptx::tma_load_3d_warp(sA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BLOCK_K, t0 + tap - a.pad, b0);
-                    ptx::tma_load_2d_warp(sW + stage * C::W_STAGE_BYTES, &tmW, &full[stage], tap * a.Cp + kc * BLOCK_K, n0);
+                    ptx::tma_load_2d_warp(sW + stage * C::W_STAGE_BYTES, half ? &tmWh : &tmW, &full[stage], tap * a.Cp + kc * BLOCK_K, n0);
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -122,6 +139,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
             ptx::mbar_wait(&tempty[as], aphase ^ 1);
             ptx::tc_fence_after();
+            const uint32_t idesc = tile < a.full_tiles ? a.idesc : a.idesc_half;
             const uint32_t d_tmem = tmem_base + (uint32_t)(as * C::ACC_STRIDE);
             for (int kb = 0; kb < num_kb; ++kb) {
                 ptx::mbar_wait(&full[stage], phase);
@@ -131,7 +149,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                     // advance 32 bytes (16 elements) along K inside the swizzle row: +2 in the (addr>>4) field
-                    ptx::umma_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, (kb | k) != 0 ? 1u : 0u);
+                    ptx::umma_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
                 }
                 ptx::umma_commit_warp(&empty[stage]);
                 if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
@@ -145,12 +163,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int r = q * 32 + lane;            // tile row
         int as = 0; uint32_t aphase = 0;
         for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-            const int nt = tile % a.tiles_n, mt = tile / a.tiles_n;
+            int mt, n0, bn;
+            decode_tile<BLOCK_N>(a, tile, mt, n0, bn);
             const int t = (mt % a.tiles_t) * a.TB + (r % a.TB);
             const int b = (mt / a.tiles_t) * a.BB + (r / a.TB);
             const bool valid = (t < a.gT) && (b < a.gB);
             const size_t m = (size_t)b * a.gT + t;
-            const int n0 = nt * BLOCK_N;
             // channel-first addressing uses the true utterance length
             size_t ot_base = 0;
             if (a.out_t) { const size_t bb = m / a.T, tt = m - bb * a.T; ot_base = (bb * a.N) * a.T + tt; }
@@ -168,7 +186,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 uint8_t* stg = sOut + q * 2 * OUT_STAGE_BYTES;
                 const uint32_t my_row = ptx::smem_u32(stg) + (uint32_t)(lane * 128);
 #pragma unroll 1
-                for (int c0 = 0; c0 < BLOCK_N; c0 += cw) {
+                for (int c0 = 0; c0 < bn; c0 += cw) {
                     const uint32_t buf = (uint32_t)((c0 / cw) & 1) * OUT_STAGE_BYTES;
                     if (lane == 0) ptx::bulk_wait_group_read<1>();           // the store that last read this buffer is done
                     __syncwarp();
@@ -227,7 +245,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             } else
 #pragma unroll 1
-            for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
+            for (int c0 = 0; c0 < bn; c0 += 16) {
                 uint32_t rr[16];
                 ptx::tmem_ld16(taddr + (uint32_t)c0, rr);
                 ptx::tmem_ld_wait();
@@ -300,7 +318,7 @@ EncodeTiledFn g_encode = nullptr;
 }  // namespace
 
 struct TcGemmPlan {
-    CUtensorMap tmA, tmW, tmO;
+    CUtensorMap tmA, tmW, tmO, tmWh;
     TcGemmArgs args;
     int block_n;
     int grid;
@@ -363,6 +381,15 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
     a.tiles_n = p.N / bn;
     a.num_tiles = tiles_m * a.tiles_n;
     plan->grid = a.num_tiles < num_sms ? a.num_tiles : num_sms;
+    a.full_tiles = a.num_tiles;
+    {   // split the tiles of a mostly idle last round into half-width tiles (see decode_tile)
+        const int rem = a.num_tiles % plan->grid;
+        if (bn == 256 && a.num_tiles > plan->grid && rem > 0 && 2 * rem <= plan->grid && !getenv("AVC_GEMM_NO_TAIL_SPLIT")) {
+            a.full_tiles = a.num_tiles - rem;
+            a.num_tiles = a.full_tiles + 2 * rem;
+        }
+    }
+    a.idesc_half = ptx::umma_idesc_f16(p.a_type == DT_BF16 ? 1 : 0, BLOCK_M, bn / 2 >= 16 ? bn / 2 : 16);
     a.idesc = ptx::umma_idesc_f16(p.a_type == DT_BF16 ? 1 : 0, BLOCK_M, bn);
 
     // ---- tensor maps ----
@@ -385,6 +412,13 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
         CUresult r = g_encode(&plan->tmW, dt, 2, const_cast<void*>(p.W), gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(W) failed: %d", (int)r); return bad(msg); }
+        plan->tmWh = plan->tmW;
+        if (a.full_tiles < a.num_tiles) {
+            box[1] = (cuuint32_t)(bn / 2);
+            r = g_encode(&plan->tmWh, dt, 2, const_cast<void*>(p.W), gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(W half) failed: %d", (int)r); return bad(msg); }
+        }
     }
     // ---- row-major output through TMA stores: one box = an epilogue warp's 32 tile rows x 128 bytes ----
     a.tma_out = 0;
@@ -415,9 +449,9 @@ cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t,
     args.out_t = out_t;
     args.res_t = res_t;
     switch (plan->block_n) {
-        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, args); break;
-        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, args); break;
-        default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, args); break;
+        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
+        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
+        default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
     }
     return cudaGetLastError();
 }

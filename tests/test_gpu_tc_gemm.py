@@ -93,3 +93,25 @@ def test_simt_gemm_agrees_with_tc(engine, layer, cin, dtype, act, chan_first):
     engine.debug_gemm(layer, A, T, act, out, False)
     torch.cuda.synchronize()
     assert float((out.float() - ref).abs().max()) <= 2e-2 * max(1.0, float(ref.abs().max()))
+
+
+@pytest.mark.parametrize("layer,cin,dtype,act", [("enc.conv1", 512, torch.bfloat16, 1), ("post.conv2", 512, torch.float16, 2)])
+def test_tail_round_split_into_half_tiles(engine, layer, cin, dtype, act):
+    """N=512 layers at B*T = 100 x 128 rows: 200 tiles of 128x256 on 148 CTAs leave a last round of 52 tiles, which the
+    static schedule splits into 104 half-width tiles (tc_gemm.cu::decode_tile).  Results must not depend on the split."""
+    import os
+    B, T = 100, 128
+    A = (torch.rand(B * T, cin, device="cuda") * 2 - 1).to(dtype).contiguous()
+    ref = reference(engine, layer, A, B, T, act, dtype)
+    out = torch.full((B * T, 512), float("nan"), device="cuda", dtype=dtype)
+    engine.debug_gemm(layer, A, T, act, out, True)
+    torch.cuda.synchronize()
+    assert float((out.float() - ref).abs().max()) <= 2e-2 * max(1.0, float(ref.abs().max()))
+    os.environ["AVC_GEMM_NO_TAIL_SPLIT"] = "1"
+    try:
+        out2 = torch.full_like(out, float("nan"))
+        engine.debug_gemm(layer, A, T, act, out2, True)
+        torch.cuda.synchronize()
+    finally:
+        del os.environ["AVC_GEMM_NO_TAIL_SPLIT"]
+    assert torch.equal(out, out2)
