@@ -69,7 +69,9 @@ class Engine:
             self._ws = torch.empty(need, dtype=torch.uint8, device=torch.device("cuda", self.device_index))
         return self._ws
 
-    def forward(self, x: torch.Tensor, c_org: torch.Tensor, c_trg: Optional[torch.Tensor]):
+    def forward(self, x: torch.Tensor, c_org: torch.Tensor, c_trg: Optional[torch.Tensor], out=None):
+        """`out`: optional preallocated (mel, mel_post, codes) float32 CUDA tensors of the result shapes (steady-state
+        pipelines that must not touch the allocator); default: fresh tensors, like the reference."""
         B, n_mels, T = x.shape
         dn, E, _, freq = self.dims
         if n_mels != 80 or c_org.shape != (B, E) or (c_trg is not None and c_trg.shape != (B, E)):
@@ -87,8 +89,14 @@ class Engine:
                                     ws.numel(), stream)
             L.raise_for(rc, self._h)
             return codes
-        mel = torch.empty(B, 80, T, dtype=torch.float32, device=dev)
-        post = torch.empty(B, 80, T, dtype=torch.float32, device=dev)
+        if out is not None:
+            mel, post, codes = out
+            for t, shp in ((mel, (B, 80, T)), (post, (B, 80, T)), (codes, (B, n_codes))):
+                if tuple(t.shape) != shp or t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+                    raise RuntimeError(f"out tensors must be contiguous float32 on {dev} with shapes (B,80,T), (B,80,T), (B,{n_codes})")
+        else:
+            mel = torch.empty(B, 80, T, dtype=torch.float32, device=dev)
+            post = torch.empty(B, 80, T, dtype=torch.float32, device=dev)
         rc = L.lib().avc_forward(self._h, x.data_ptr(), c_org.data_ptr(), c_trg.data_ptr(), B, T, mel.data_ptr(),
                                  post.data_ptr(), codes.data_ptr(), ws.data_ptr(), ws.numel(), stream)
         L.raise_for(rc, self._h)
@@ -179,6 +187,7 @@ _lib_def = torch.library.Library("autovc_b200", "DEF")
 _lib_def.define("generator_forward(Tensor x, Tensor c_org, Tensor c_trg, int engine) -> (Tensor, Tensor, Tensor)")
 _lib_def.define("generator_encode(Tensor x, Tensor c_org, int engine) -> Tensor")
 _lib_def.define("speaker_embed(Tensor partials, int engine) -> Tensor")
+_lib_def.define("generator_forward_out(Tensor x, Tensor c_org, Tensor c_trg, Tensor(a!) mel, Tensor(b!) post, Tensor(c!) codes, int engine) -> ()")
 
 
 def _prep(t: torch.Tensor) -> torch.Tensor:
@@ -193,6 +202,10 @@ def _encode_cuda(x, c_org, engine: int):
     return _ENGINES[engine].forward(_prep(x), _prep(c_org), None)
 
 
+def _forward_out_cuda(x, c_org, c_trg, mel, post, codes, engine: int):
+    _ENGINES[engine].forward(_prep(x), _prep(c_org), _prep(c_trg), out=(mel, post, codes))
+
+
 def _speaker_embed_cuda(partials, engine: int):
     return _ENGINES[engine].se_forward(_prep(partials))
 
@@ -205,7 +218,9 @@ _lib_impl_cuda = torch.library.Library("autovc_b200", "IMPL", "CUDA")
 _lib_impl_cuda.impl("generator_forward", _forward_cuda)
 _lib_impl_cuda.impl("generator_encode", _encode_cuda)
 _lib_impl_cuda.impl("speaker_embed", _speaker_embed_cuda)
+_lib_impl_cuda.impl("generator_forward_out", _forward_out_cuda)
 _lib_impl_cpu = torch.library.Library("autovc_b200", "IMPL", "CPU")
 _lib_impl_cpu.impl("generator_forward", _no_cpu)
 _lib_impl_cpu.impl("generator_encode", _no_cpu)
 _lib_impl_cpu.impl("speaker_embed", _no_cpu)
+_lib_impl_cpu.impl("generator_forward_out", _no_cpu)

@@ -131,8 +131,8 @@ class AutoEncoder(nn.Module):
         return eng
 
     # -- the path ----------------------------------------------------------------------------------
-    def forward(self, x: torch.Tensor, c_org: torch.Tensor, c_trg: Optional[torch.Tensor]):
-        """reference `AutoEncoder.forward` (`model.py:68-146`).
+    def forward(self, x: torch.Tensor, c_org: torch.Tensor, c_trg: Optional[torch.Tensor], out=None):
+        """reference `AutoEncoder.forward` (`model.py:68-146`).  `out` (extension): preallocated (mel, mel_post, codes) to fill.
 
         x (B,80,T) float, c_org/c_trg (B,dim_emb) -> (mel_outputs (B,80,T), mel_outputs_postnet (B,80,T),
         content_codes (B, dim_neck*(T//freq + ceil(T/freq)))); with `c_trg is None` only content_codes.
@@ -143,6 +143,9 @@ class AutoEncoder(nn.Module):
         c_org = c_org.to(x.device)
         if c_trg is None:
             return torch.ops.autovc_b200.generator_encode(x, c_org, eng.id)
+        if out is not None:
+            torch.ops.autovc_b200.generator_forward_out(x, c_org, c_trg.to(x.device), out[0], out[1], out[2], eng.id)
+            return out
         mel, post, codes = torch.ops.autovc_b200.generator_forward(x, c_org, c_trg.to(x.device), eng.id)
         return mel, post, codes
 

@@ -220,7 +220,7 @@ def main():
     pipe = HostPipeline(model, dev)
     host_in = [(x_h, co_h, ct_h)] * K
     host_out = [(mel_h, post_h, codes_h)] * K
-    pipe.run(host_in[:2], host_out[:2])
+    pipe.run(host_in[:max(2, min(K, 6))], host_out[:max(2, min(K, 6))])   # untimed: fills the allocator's pools for both streams
     barrier()
     e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     flush.zero_()

@@ -160,3 +160,16 @@ def test_outputs_do_not_alias_cached_plans():
     for mel, post, codes in keep[1:]:
         assert torch.equal(post, keep[0][1]) and torch.equal(mel, keep[0][0]) and torch.equal(codes, keep[0][2])
     assert float(keep[2][1].abs().max()) > 1.0
+
+
+def test_forward_into_preallocated_outputs():
+    """`out=` (extension used by HostPipeline so that its steady state never touches the allocator) fills caller tensors
+    with exactly what the allocating call returns, and rejects tensors of the wrong shape."""
+    m = model("bf16")
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(3, 100, seed=4))
+    mel, post, codes = m(x, c_org, c_trg)
+    out = (torch.full_like(mel, float("nan")), torch.full_like(post, float("nan")), torch.full_like(codes, float("nan")))
+    res = m(x, c_org, c_trg, out=out)
+    assert res[0] is out[0] and torch.equal(out[0], mel) and torch.equal(out[1], post) and torch.equal(out[2], codes)
+    with pytest.raises(RuntimeError):
+        m(x, c_org, c_trg, out=(out[0][:2], out[1], out[2]))
