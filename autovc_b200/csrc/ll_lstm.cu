@@ -125,19 +125,26 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
-template <int NKB, bool GXH>
+template <int NKB, bool GXH, int TN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     constexpr int NKB_T = NKB < MAX_TMEM_CHUNKS ? NKB : MAX_TMEM_CHUNKS;   // W chunks resident in tensor memory
     constexpr int NKB_S = NKB - NKB_T;                                     // W chunks resident in shared memory
     constexpr int WPC = LOAD_WARPS / NKB;                                  // loader warps per chunk: 1, 2 or 4
+    // TN = utterances per CTA pair = UMMA N.  64 fills the machine at B = 256; 32 is used when the batch leaves room for twice
+    // the tiles: a step is a latency chain, and half the tile halves its MMA, load and epilogue stretches.
+    constexpr int ROWS = TN / 2;                          // utterance rows of h staged by one CTA of the pair
+    constexpr int HBLK = ROWS * KBLK * 2;                 // bytes per CTA and chunk of the operand tile
+    constexpr int PSTRIDE = TN * PLANE_ELEMS;             // elements between planes of Yx
+    constexpr int CPT = TN / 2;                           // accumulator columns (utterances) per epilogue thread
+    static_assert(TN == 64 || TN == 32, "tile of 64 or 32 utterances");
     static_assert(NKB == 16 || NKB == 8 || NKB == 4, "H must be 1024, 512 or 256");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sW = smem;                                        // NKB_S x 16 KiB: W columns beyond the TMEM-resident part
     uint8_t* sH = sW + NKB_S * W_BLK_BYTES;                    // NKB x 4 KiB: this CTA's 32 rows of the h_{t-1} operand tiles
-    uint8_t* sGx = sH + NKB * H_BLK_BYTES;                     // 32 KiB
+    uint8_t* sGx = sH + NKB * HBLK;                     // 32 KiB
     uint8_t* sHT = sGx + GX_BYTES;                             // 4 KiB
     uint64_t* bars = reinterpret_cast<uint64_t*>(sHT + HT_BYTES);
     uint64_t* wfull = bars;
@@ -149,9 +156,9 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp: provably uniform
     const int ns = blockIdx.x;            // unit slice (32 units)
     const int bt = blockIdx.y;            // batch tile (64 utterances)
-    const int b0 = bt * TILE_N;
+    const int b0 = bt * TN;
     const uint32_t crank = ptx::cluster_ctarank();   // 0 = leader of the CTA pair (adjacent unit slices, same batch tile)
-    const size_t tile_elems = (size_t)a.H * TILE_N;                         // one (t, tile) block of Yx
+    const size_t tile_elems = (size_t)a.H * TN;                         // one (t, tile) block of Yx
     const size_t step_elems = tile_elems * a.tiles;
     __nv_bfloat16* yx_tile = a.Yx + (size_t)(a.tile0 + bt) * tile_elems;    // + t * step_elems
 
@@ -205,61 +212,58 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         const bool epi = warp < EPI_WARPS;
         // ---- loader geometry: this warp's chunk and, per piece i, the (row, plane) of the lane ----
         const int kc = warp / WPC, sub = warp % WPC;
-        constexpr int NP = NKB / 2;                           // 16-byte pieces per lane and step: 32 rows x 8 planes x NKB chunks / 512
-        auto piece_row = [&](int i) { return WPC == 1 ? lane : (WPC == 2 ? sub * 16 + (lane & 15) : sub * 8 + (lane & 7)); };
-        auto piece_plane = [&](int i) { return WPC == 1 ? i : (WPC == 2 ? 2 * i + (lane >> 4) : 4 * i + (lane >> 3)); };
-        const uint32_t sH_chunk = ptx::smem_u32(sH) + (uint32_t)(kc * H_BLK_BYTES);
-        const __nv_bfloat16* chunk_base = yx_tile + (size_t)kc * 8 * PLANE_STRIDE + (size_t)(crank * ROWS_CTA) * PLANE_ELEMS;
+        constexpr int NP = ROWS * 8 * NKB / NUM_THREADS;      // 16-byte pieces per lane and step: ROWS rows x 8 planes x NKB chunks / 512
+        auto piece_row = [&](int i) {
+            if constexpr (TN == 64) return WPC == 1 ? lane : (WPC == 2 ? sub * 16 + (lane & 15) : sub * 8 + (lane & 7));
+            else return lane & 15;
+        };
+        auto piece_plane = [&](int i) {
+            if constexpr (TN == 64) return WPC == 1 ? i : (WPC == 2 ? 2 * i + (lane >> 4) : 4 * i + (lane >> 3));
+            else return sub * (8 / WPC) + 2 * i + (lane >> 4);
+        };
+        const uint32_t sH_chunk = ptx::smem_u32(sH) + (uint32_t)(kc * HBLK);
+        const __nv_bfloat16* chunk_base = yx_tile + (size_t)kc * 8 * PSTRIDE + (size_t)(crank * ROWS) * PLANE_ELEMS;
 
         // ---- epilogue geometry ----
-        const int q = warp & 3, half = (warp >> 2) & 1;       // TMEM lane quarter; utterance half (32 columns)
+        const int q = warp & 3, half = (warp >> 2) & 1;       // TMEM lane quarter; utterance half (CPT columns)
         const int R = q * 32 + lane;                          // gate row of this CTA = TMEM lane
         const int gj = lane & 3;                              // gate of this lane: 0=i 1=f 2=g 3=o
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 32);
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * CPT);
         const float act_s = gj == 2 ? 2.0f : 1.0f, act_o = gj == 2 ? -1.0f : 0.0f;   // tanh(x) = 2 sigmoid(2x) - 1
-        float c[8];
+        float c[CPT / 4];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) c[k] = 0.0f;
+        for (int k = 0; k < CPT / 4; ++k) c[k] = 0.0f;
         const uint32_t gx_smem = ptx::smem_u32(sGx);
         const uint32_t ht_smem = ptx::smem_u32(sHT);
         // Gx staging: thread e copies 16-byte pieces e + 256 i of the tile's [utterance][gate row] block
         auto stage_gx = [&](int t) {
             const size_t toff = (size_t)(t / a.gx_div) * a.gx_st + (size_t)ns * MROWS;
-            if constexpr (GXH) {      // fp16: 256 bytes per utterance
+            constexpr int ES = GXH ? 2 : 4, SEGS = MROWS * ES / 16;       // 16-byte pieces per utterance: 16 (fp16) or 32 (fp32)
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int id = threadIdx.x + EPI_THREADS * i;
-                    const int u = id >> 4, seg = id & 15;
-                    const int b = b0 + u < a.B ? b0 + u : a.B - 1;
-                    cp_async16(gx_smem + (uint32_t)(u * (MROWS * 2) + seg * 16),
-                               reinterpret_cast<const __half*>(a.Gx) + (size_t)b * a.gx_sb + toff + seg * 8);
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int id = threadIdx.x + EPI_THREADS * i;
-                    const int u = id >> 5, seg = id & 31;
-                    const int b = b0 + u < a.B ? b0 + u : a.B - 1;
-                    cp_async16(gx_smem + (uint32_t)(u * (MROWS * 4) + seg * 16),
-                               reinterpret_cast<const float*>(a.Gx) + (size_t)b * a.gx_sb + toff + seg * 4);
-                }
+            for (int i = 0; i < TN * SEGS / EPI_THREADS; ++i) {
+                const int id = threadIdx.x + EPI_THREADS * i;
+                const int u = id / SEGS, seg = id % SEGS;
+                const int b = b0 + u < a.B ? b0 + u : a.B - 1;
+                cp_async16(gx_smem + (uint32_t)(u * (MROWS * ES) + seg * 16),
+                           reinterpret_cast<const char*>(a.Gx) + ((size_t)b * a.gx_sb + toff) * ES + seg * 16);
             }
             cp_async_commit();
         };
         auto gx_at = [&](int k) -> float {      // Gx_t[utterance half*32 + k][gate row R]
             if constexpr (GXH) {
                 uint16_t hbits;
-                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hbits) : "r"(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 2)));
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hbits) : "r"(gx_smem + (uint32_t)(((half * CPT + k) * MROWS + R) * 2)));
                 return __half2float(__ushort_as_half(hbits));
             } else {
-                return ld_shared_f32(gx_smem + (uint32_t)(((half * 32 + k) * MROWS + R) * 4));
+                return ld_shared_f32(gx_smem + (uint32_t)(((half * CPT + k) * MROWS + R) * 4));
             }
         };
-        // output geometry of the final 16-byte stores: thread e -> utterance e/4, 8-unit piece e%4
-        const int ou = threadIdx.x >> 2, op = threadIdx.x & 3;
-        const bool ovalid = b0 + ou < a.B;
+        // output geometry of the final 16-byte stores: threads e < 4 TN -> utterance e/4, 8-unit piece e%4
+        const int ou = (threadIdx.x >> 2) & (TN - 1), op = threadIdx.x & 3;
+        const bool ostore = threadIdx.x < TN * 4;
+        const bool ovalid = ostore && b0 + ou < a.B;
         __nv_bfloat16* y_out = a.Y + (size_t)(ovalid ? b0 + ou : 0) * a.y_sb + (size_t)ns * SLICE_UNITS + op * 8;
-        __nv_bfloat16* yx_out = yx_tile + ((size_t)(ns * 4 + op) * TILE_N + (ou & (TILE_N - 1))) * PLANE_ELEMS;
+        __nv_bfloat16* yx_out = yx_tile + ((size_t)(ns * 4 + op) * TN + ou) * PLANE_ELEMS;
         if (epi) stage_gx(0);
 
         for (int t = 0; t < a.T; ++t) {
@@ -271,7 +275,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 // the wave would be a second L2 round trip (~2k cycles under load) per step.  Loader-only warps arrive a whole epilogue
                 // early; a single 16-byte canary per lane keeps them off the fabric until their producers have stored.
                 if (epi ? a.canary >= 2 : a.canary >= 1) {
-                    const __nv_bfloat16* p = src + (size_t)piece_plane(0) * PLANE_STRIDE + piece_row(0) * PLANE_ELEMS;
+                    const __nv_bfloat16* p = src + (size_t)piece_plane(0) * PSTRIDE + piece_row(0) * PLANE_ELEMS;
                     uint4 cn = ld_strong(p);
                     for (uint32_t spin = 0; unwritten(cn); ++spin) {
                         cn = ld_strong(p);
@@ -282,7 +286,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 uint4 v[NP];
 #pragma unroll
                 for (int i = 0; i < NP; ++i)
-                    v[i] = ld_strong(src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS);
+                    v[i] = ld_strong(src + (size_t)piece_plane(i) * PSTRIDE + piece_row(i) * PLANE_ELEMS);
                 if (epi) stage_gx(t);                  // Gx_t is needed a whole MMA phase from now: issue it behind the h loads
                 // the MMAs of step t-1 still read the tiles until acc_full(t-1): normally long past
                 if (t >= 2 && !epi) ptx::mbar_wait(acc_full, (uint32_t)(t - 2) & 1);
@@ -291,7 +295,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 #pragma unroll
                     for (int i = 0; i < NP; ++i)
                         if (unwritten(v[i])) {
-                            v[i] = ld_strong(src + (size_t)piece_plane(i) * PLANE_STRIDE + piece_row(i) * PLANE_ELEMS);
+                            v[i] = ld_strong(src + (size_t)piece_plane(i) * PSTRIDE + piece_row(i) * PLANE_ELEMS);
                             missing = true;
                         }
                     if (!missing) break;
@@ -327,7 +331,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                         for (int cc = 0; cc < NKB / 4; ++cc) {
                             const int c = g * (NKB / 4) + cc;
                             const uint32_t first = (gg | cc) == 0 ? 0u : 1u;
-                            const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sH) + (uint32_t)(c * H_BLK_BYTES));
+                            const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sH) + (uint32_t)(c * HBLK));
                             if (c < NKB_T) {
                                 const uint32_t a_tmem = tmem_base + W_COL0 + (uint32_t)(c * 32);
 #pragma unroll
@@ -351,32 +355,33 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             // ---- epilogue: gates, cell state, h_t ----
             cp_async_wait_all();                       // own pieces of Gx_t ...
             named_bar_sync(2, EPI_THREADS);            // ... and everybody else's
-            float act[32];
+            float act[CPT];
             if (t >= 1) {
                 ptx::mbar_wait(acc_full, (uint32_t)(t - 1) & 1);
                 if (threadIdx.x == 0) AVC_TRACE(4);
                 ptx::tc_fence_after();
-                uint32_t acc0[2][16], acc1[2][16];
-                ptx::tmem_ld16(taddr, acc0[0]);
-                ptx::tmem_ld16(taddr + 16, acc0[1]);
-                ptx::tmem_ld16(taddr + TILE_N, acc1[0]);
-                ptx::tmem_ld16(taddr + TILE_N + 16, acc1[1]);
+                uint32_t acc0[CPT / 16][16], acc1[CPT / 16][16];
+#pragma unroll
+                for (int j = 0; j < CPT / 16; ++j) {
+                    ptx::tmem_ld16(taddr + (uint32_t)(16 * j), acc0[j]);
+                    ptx::tmem_ld16(taddr + (uint32_t)(TILE_N + 16 * j), acc1[j]);
+                }
                 ptx::tmem_ld_wait();
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive_cluster(acc_empty, 0u);
 #pragma unroll
-                for (int k = 0; k < 32; ++k) act[k] = __uint_as_float(acc0[k >> 4][k & 15]) + __uint_as_float(acc1[k >> 4][k & 15]);
+                for (int k = 0; k < CPT; ++k) act[k] = __uint_as_float(acc0[k >> 4][k & 15]) + __uint_as_float(acc1[k >> 4][k & 15]);
             } else {
 #pragma unroll
-                for (int k = 0; k < 32; ++k) act[k] = 0.0f;
+                for (int k = 0; k < CPT; ++k) act[k] = 0.0f;
             }
-            // + Gx_t[utterance half*32 + k][gate row R], then this lane's activation
+            // + Gx_t[utterance half*CPT + k][gate row R], then this lane's activation
             if (a.approx) {
                 // sigmoid(x) = 0.5 tanh(0.5 x) + 0.5, tanh(x) as is: one MUFU.TANH per gate value
                 const float ps = gj == 2 ? 1.0f : 0.5f, po = gj == 2 ? 0.0f : 0.5f;
 #pragma unroll
-                for (int k = 0; k < 32; ++k) {
+                for (int k = 0; k < CPT; ++k) {
                     const float x = act[k] + gx_at(k);
                     float th;
                     asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(ps * x));
@@ -384,29 +389,30 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 }
             } else {
 #pragma unroll
-                for (int k = 0; k < 32; ++k) {
+                for (int k = 0; k < CPT; ++k) {
                     const float x = act[k] + gx_at(k);
                     act[k] = __fdividef(act_s, 1.0f + __expf(-act_s * x)) + act_o;
                 }
             }
             if (threadIdx.x == 0) AVC_TRACE(6);
-            // 4x4 quad transpose (blocks of 8 columns): lane j ends with all four gates of columns 8j..8j+7
-            float X[16], Y2[16];
+            // 4x4 quad transpose (blocks of CPT/4 columns): lane j ends with all four gates of columns (CPT/4) j .. (CPT/4) j + CPT/4 - 1
+            constexpr int H1 = CPT / 2, H2 = CPT / 4;
+            float X[H1], Y2[H1];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const float send = (gj & 2) ? act[k] : act[16 + k];
-                X[k] = (gj & 2) ? act[16 + k] : act[k];                      // own gate gj
+            for (int k = 0; k < H1; ++k) {
+                const float send = (gj & 2) ? act[k] : act[H1 + k];
+                X[k] = (gj & 2) ? act[H1 + k] : act[k];                      // own gate gj
                 Y2[k] = __shfl_xor_sync(0xffffffffu, send, 2);               // gate gj ^ 2
             }
-            uint32_t hp[4];
+            uint32_t hp[H2 / 2];
 #pragma unroll
-            for (int k = 0; k < 8; k += 2) {
+            for (int k = 0; k < H2; k += 2) {
                 float hv[2];
 #pragma unroll
                 for (int w = 0; w < 2; ++w) {
                     const int kk = k + w;
-                    const float sx = (gj & 1) ? X[kk] : X[8 + kk], sy = (gj & 1) ? Y2[kk] : Y2[8 + kk];
-                    const float kx = (gj & 1) ? X[8 + kk] : X[kk], ky = (gj & 1) ? Y2[8 + kk] : Y2[kk];
+                    const float sx = (gj & 1) ? X[kk] : X[H2 + kk], sy = (gj & 1) ? Y2[kk] : Y2[H2 + kk];
+                    const float kx = (gj & 1) ? X[H2 + kk] : X[kk], ky = (gj & 1) ? Y2[H2 + kk] : Y2[kk];
                     const float rx = __shfl_xor_sync(0xffffffffu, sx, 1), ry = __shfl_xor_sync(0xffffffffu, sy, 1);
                     // kx: gate gj, ky: gj^2, rx: gj^1, ry: gj^3
                     const float e0 = (gj & 1) ? rx : kx, e2 = (gj & 1) ? ry : ky;     // gates (gj & 2) and (gj & 2) ^ 2
@@ -427,8 +433,8 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             {
                 const int unit = q * 8 + (lane >> 2);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const int u = half * 32 + gj * 8 + k;
+                for (int k = 0; k < H2; ++k) {
+                    const int u = half * CPT + gj * H2 + k;
                     const int piece = (unit >> 3) ^ ((u >> 3) & 3);
                     const uint16_t hv16 = (uint16_t)((k & 1) ? (hp[k >> 1] >> 16) : (hp[k >> 1] & 0xffffu));
                     st_shared_u16(ht_smem + (uint32_t)(u * 64 + piece * 16 + (unit & 7) * 2), hv16);
@@ -436,7 +442,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             }
             named_bar_sync(1, EPI_THREADS);
             if (threadIdx.x == 0) AVC_TRACE(8);
-            {
+            if (ostore) {
                 const uint4 hv4 = ld_shared_v4(ht_smem + (uint32_t)(ou * 64 + ((op ^ ((ou >> 3) & 3)) << 4)));
                 // utterances beyond B hold bounded garbage: they are exchanged like any other row, so loaders need no
                 // row masks, and they are never written to Y
@@ -461,13 +467,15 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode_ll = nullptr;
 
-const void* kernel_for(int nkb, bool gxh) {
+template <int TN>
+const void* kernel_for_tn(int nkb, bool gxh) {
     switch (nkb) {
-        case 16: return gxh ? (const void*)ll_lstm_kernel<16, true> : (const void*)ll_lstm_kernel<16, false>;
-        case 8: return gxh ? (const void*)ll_lstm_kernel<8, true> : (const void*)ll_lstm_kernel<8, false>;
-        default: return gxh ? (const void*)ll_lstm_kernel<4, true> : (const void*)ll_lstm_kernel<4, false>;
+        case 16: return gxh ? (const void*)ll_lstm_kernel<16, true, TN> : (const void*)ll_lstm_kernel<16, false, TN>;
+        case 8: return gxh ? (const void*)ll_lstm_kernel<8, true, TN> : (const void*)ll_lstm_kernel<8, false, TN>;
+        default: return gxh ? (const void*)ll_lstm_kernel<4, true, TN> : (const void*)ll_lstm_kernel<4, false, TN>;
     }
 }
+const void* kernel_for(int nkb, bool gxh, int tn) { return tn == 32 ? kernel_for_tn<32>(nkb, gxh) : kernel_for_tn<64>(nkb, gxh); }
 
 int smem_for(int nkb) {
     const int nkb_s = nkb > MAX_TMEM_CHUNKS ? nkb - MAX_TMEM_CHUNKS : 0;
@@ -480,7 +488,7 @@ struct LlLstmPlan {
     CUtensorMap tmW;
     std::vector<LlLstmArgs> args;
     std::vector<dim3> grids;
-    int nkb;
+    int nkb, tn;
     bool gx_f16;
     int smem_bytes;
     void* yx_base; size_t yx_bytes;       // region to pre-fill with the "unwritten" pattern before every launch
@@ -492,8 +500,9 @@ const char* ll_lstm_init() {
     cudaDriverEntryPointQueryResult qres;
     cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
     if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return "cuTensorMapEncodeTiled not available from the driver";
-    for (int i = 0; i < 6; ++i)
-        if (cudaFuncSetAttribute(kernel_for(4 << (i >> 1), i & 1), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_for(4 << (i >> 1))) != cudaSuccess)
+    for (int i = 0; i < 12; ++i)
+        if (cudaFuncSetAttribute(kernel_for(4 << ((i >> 1) % 3), i & 1, i < 6 ? 64 : 32), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 smem_for(4 << ((i >> 1) % 3))) != cudaSuccess)
             return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed for ll_lstm_kernel";
     g_encode_ll = reinterpret_cast<EncodeTiledFn>(fn);
     return nullptr;
@@ -514,7 +523,11 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
     plan->nkb = nkb;
     plan->smem_bytes = smem_for(nkb);
     plan->gx_f16 = gx_type == DT_F16;
-    plan->yx_base = Yx; plan->yx_bytes = ll_lstm_exchange_bytes(B, T, H);
+    // tile width: 32 utterances per CTA pair when twice the tiles still fit the machine (small batches: shorter steps)
+    int tn = ceil_div(B, 32) * G_n <= (num_sms & ~1) ? 32 : 64;
+    if (const char* tv = getenv("AVC_LSTM_TN")) tn = atoi(tv) == 32 ? 32 : 64;
+    plan->tn = tn;
+    plan->yx_base = Yx; plan->yx_bytes = (size_t)T * ceil_div(B, tn) * tn * H * 2;
     {
         cuuint64_t gdim[2] = {(cuuint64_t)H, (cuuint64_t)4 * H};
         cuuint64_t gstr[1] = {(cuuint64_t)H * 2};
@@ -526,7 +539,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(Whh) failed: %d", (int)r); return bad(msg); }
     }
     const int tiles_per_launch = (num_sms & ~1) / G_n;
-    const int rows_per_launch = tiles_per_launch * TILE_N;
+    const int rows_per_launch = tiles_per_launch * tn;
     for (int bs = 0; bs < B; bs += rows_per_launch) {
         const int Bc = (B - bs) < rows_per_launch ? (B - bs) : rows_per_launch;
         LlLstmArgs a{};
@@ -536,12 +549,12 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         a.Whh = reinterpret_cast<const __nv_bfloat16*>(Whh_bf16);
         a.Y = reinterpret_cast<__nv_bfloat16*>(Y) + (size_t)bs * a.y_sb;
         a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
-        a.tiles = ceil_div(B, TILE_N); a.tile0 = bs / TILE_N;
+        a.tiles = ceil_div(B, tn); a.tile0 = bs / tn;
         a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
         { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : 1; }
-        a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, TILE_N);      // the pair's MMA: M = 256 (128 gate rows per CTA), N = 64
+        a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, tn);          // the pair's MMA: M = 256 (128 gate rows per CTA), N = tile width
         plan->args.push_back(a);
-        plan->grids.push_back(dim3(G_n, ceil_div(Bc, TILE_N)));
+        plan->grids.push_back(dim3(G_n, ceil_div(Bc, tn)));
     }
     return plan;
 }
@@ -570,7 +583,7 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
         // AVC_LSTM_NOCOOP: profiling aid (ncu refuses cooperative cluster launches); the grid is sized to be
         // co-resident either way, the attribute only makes the driver check it
         cfg.attrs = at; cfg.numAttrs = getenv("AVC_LSTM_NOCOOP") ? 1 : 2;
-        e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb, plan->gx_f16), kargs);
+        e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb, plan->gx_f16, plan->tn), kargs);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
         if (tracing) {   // debugging aid: synchronous dump of the per-step timeline of CTA (0,0)
