@@ -37,6 +37,7 @@
 // Every spin/wait is bounded: a protocol bug traps (CUDA error) instead of hanging the GPU.
 #include <cstdio>
 #include <cstdlib>
+#include <type_traits>
 #include <vector>
 #include <cuda.h>
 
@@ -319,32 +320,39 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     // reproducible).  Whole-warp, uniform operands, one elected lane issues.
                     const int ih = warp - MMA_WARP0;
                     if (t >= 2) ptx::mbar_wait(acc_empty, (uint32_t)(t - 2) & 1);   // both epilogues of step t-1 have read D
-                    const uint32_t d_tmem = tmem_base + (uint32_t)(ih * TILE_N);
+                    // instantiated per issuing warp: every chunk index, TMEM address and descriptor offset is then a compile-time
+                    // constant (a runtime K half doubles the code with TS/SS branches and puts ~20 instructions between two MMAs)
+                    auto issue = [&](auto IH) {
+                        constexpr int ih_ = decltype(IH)::value;
+                        constexpr uint32_t d_tmem = tmem_base + (uint32_t)(ih_ * TILE_N);
+                        const uint32_t sH_u = ptx::smem_u32(sH), sW_u = ptx::smem_u32(sW);
 #pragma unroll
-                    for (int gg = 0; gg < 2; ++gg) {
-                        const int g = ih * 2 + gg;
-                        ptx::mbar_wait(&gfull[g], (uint32_t)(t - 1) & 1);
-                        ptx::tc_fence_after();
-                        if (g == 0) AVC_TRACE(2);
-                        AVC_TRACE(10 + g);
+                        for (int gg = 0; gg < 2; ++gg) {
+                            const int g = ih_ * 2 + gg;
+                            ptx::mbar_wait(&gfull[g], (uint32_t)(t - 1) & 1);
+                            ptx::tc_fence_after();
+                            if (g == 0) AVC_TRACE(2);
+                            AVC_TRACE(10 + g);
 #pragma unroll
-                        for (int cc = 0; cc < NKB / 4; ++cc) {
-                            const int c = g * (NKB / 4) + cc;
-                            const uint32_t first = (gg | cc) == 0 ? 0u : 1u;
-                            const uint64_t bdesc = ptx::umma_desc_sw128(ptx::smem_u32(sH) + (uint32_t)(c * HBLK));
-                            if (c < NKB_T) {
-                                const uint32_t a_tmem = tmem_base + W_COL0 + (uint32_t)(c * 32);
+                            for (int cc = 0; cc < NKB / 4; ++cc) {
+                                const int c = g * (NKB / 4) + cc;
+                                const uint32_t first = (gg | cc) == 0 ? 0u : 1u;
+                                const uint64_t bdesc = ptx::umma_desc_sw128(sH_u + (uint32_t)(c * HBLK));
+                                if (c < NKB_T) {
+                                    const uint32_t a_tmem = tmem_base + W_COL0 + (uint32_t)(c * 32);
 #pragma unroll
-                                for (int k = 0; k < KBLK / 16; ++k)
-                                    ptx::umma2_f16_ts_warp(d_tmem, a_tmem + (uint32_t)(k * 8), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
-                            } else {
-                                const uint64_t adesc = ptx::umma_desc_sw128(ptx::smem_u32(sW + (c - NKB_T) * W_BLK_BYTES));
+                                    for (int k = 0; k < KBLK / 16; ++k)
+                                        ptx::umma2_f16_ts_warp(d_tmem, a_tmem + (uint32_t)(k * 8), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
+                                } else {
+                                    const uint64_t adesc = ptx::umma_desc_sw128(sW_u + (uint32_t)((c - NKB_T) * W_BLK_BYTES));
 #pragma unroll
-                                for (int k = 0; k < KBLK / 16; ++k)
-                                    ptx::umma2_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
+                                    for (int k = 0; k < KBLK / 16; ++k)
+                                        ptx::umma2_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
+                                }
                             }
                         }
-                    }
+                    };
+                    if (ih == 0) issue(std::integral_constant<int, 0>{}); else issue(std::integral_constant<int, 1>{});
                     ptx::umma2_commit_warp(acc_full);       // -> acc_full of BOTH CTAs
                     if (ih == 1) AVC_TRACE(3); else AVC_TRACE(14);
                 }
