@@ -38,6 +38,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <type_traits>
+#include <utility>
 #include <vector>
 #include <cuda.h>
 
@@ -326,31 +327,44 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                         constexpr int ih_ = decltype(IH)::value;
                         constexpr uint32_t d_tmem = tmem_base + (uint32_t)(ih_ * TILE_N);
                         const uint32_t sH_u = ptx::smem_u32(sH), sW_u = ptx::smem_u32(sW);
-#pragma unroll
-                        for (int gg = 0; gg < 2; ++gg) {
-                            const int g = ih_ * 2 + gg;
+                        auto issue_group = [&](auto G) {
+                            constexpr int g = decltype(G)::value;
                             ptx::mbar_wait(&gfull[g], (uint32_t)(t - 1) & 1);
                             ptx::tc_fence_after();
                             if (g == 0) AVC_TRACE(2);
                             AVC_TRACE(10 + g);
+                            [&]<int... CC>(std::integer_sequence<int, CC...>) {
+                                ([&] {
+                                    constexpr int c = g * (NKB / 4) + CC;
+                                    constexpr uint32_t first = (g == ih_ * 2 && CC == 0) ? 0u : 1u;
+                                    const uint64_t bdesc = ptx::umma_desc_sw128(sH_u + (uint32_t)(c * HBLK));
+                                    // N=32 MMAs retire every 17 cycles: one block per chunk (one election, immediates) keeps the issue
+                                    // ahead of the pipe; at N=64 (33 cycles) separate MMAs measured faster (operand set-up overlaps)
+                                    if constexpr (c < NKB_T) {
+                                        constexpr uint32_t a_tmem = tmem_base + W_COL0 + (uint32_t)(c * 32);
+                                        if constexpr (TN == 32) {
+                                            ptx::umma2_f16_ts_chunk_warp<d_tmem, a_tmem>((uint32_t)bdesc, (uint32_t)(bdesc >> 32), a.idesc, first);
+                                        } else {
 #pragma unroll
-                            for (int cc = 0; cc < NKB / 4; ++cc) {
-                                const int c = g * (NKB / 4) + cc;
-                                const uint32_t first = (gg | cc) == 0 ? 0u : 1u;
-                                const uint64_t bdesc = ptx::umma_desc_sw128(sH_u + (uint32_t)(c * HBLK));
-                                if (c < NKB_T) {
-                                    const uint32_t a_tmem = tmem_base + W_COL0 + (uint32_t)(c * 32);
+                                            for (int k = 0; k < KBLK / 16; ++k)
+                                                ptx::umma2_f16_ts_warp(d_tmem, a_tmem + (uint32_t)(k * 8), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
+                                        }
+                                    } else {
+                                        const uint64_t adesc = ptx::umma_desc_sw128(sW_u + (uint32_t)((c - NKB_T) * W_BLK_BYTES));
+                                        if constexpr (TN == 32) {
+                                            ptx::umma2_f16_ss_chunk_warp<d_tmem>((uint32_t)adesc, (uint32_t)(adesc >> 32), (uint32_t)bdesc,
+                                                                                 (uint32_t)(bdesc >> 32), a.idesc, first);
+                                        } else {
 #pragma unroll
-                                    for (int k = 0; k < KBLK / 16; ++k)
-                                        ptx::umma2_f16_ts_warp(d_tmem, a_tmem + (uint32_t)(k * 8), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
-                                } else {
-                                    const uint64_t adesc = ptx::umma_desc_sw128(sW_u + (uint32_t)((c - NKB_T) * W_BLK_BYTES));
-#pragma unroll
-                                    for (int k = 0; k < KBLK / 16; ++k)
-                                        ptx::umma2_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
-                                }
-                            }
-                        }
+                                            for (int k = 0; k < KBLK / 16; ++k)
+                                                ptx::umma2_f16_warp(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), a.idesc, k != 0 ? 1u : first);
+                                        }
+                                    }
+                                }(), ...);
+                            }(std::make_integer_sequence<int, NKB / 4>{});
+                        };
+                        issue_group(std::integral_constant<int, ih_ * 2>{});
+                        issue_group(std::integral_constant<int, ih_ * 2 + 1>{});
                     };
                     if (ih == 0) issue(std::integral_constant<int, 0>{}); else issue(std::integral_constant<int, 1>{});
                     ptx::umma2_commit_warp(acc_full);       // -> acc_full of BOTH CTAs

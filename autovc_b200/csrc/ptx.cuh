@@ -170,6 +170,47 @@ __device__ __forceinline__ void umma2_f16_ts_warp(uint32_t d_tmem, uint32_t a_tm
         ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// One 64-wide K chunk = four K=16 pair MMAs in one block: one election, TMEM addresses as immediates, the B descriptor
+// advanced inside (+2 per K step in the address field): fewer issue slots per MMA than four separate calls.
+template <uint32_t D_TMEM, uint32_t A_TMEM>
+__device__ __forceinline__ void umma2_f16_ts_chunk_warp(uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t accumulate_first) {
+    asm volatile(
+        "{\n\t.reg .pred p, q, one;\n\t.reg .b32 d, a0, a1, a2, a3, l1, l2, l3;\n\t.reg .b64 b0, b1, b2, b3;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %3, 0;\n\t"
+        "setp.eq.b32 one, 0, 0;\n\t"
+        "mov.u32 d, %4;\n\t"
+        "mov.u32 a0, %5;\n\tadd.u32 a1, a0, 8;\n\tadd.u32 a2, a0, 16;\n\tadd.u32 a3, a0, 24;\n\t"
+        "add.u32 l1, %0, 2;\n\tadd.u32 l2, %0, 4;\n\tadd.u32 l3, %0, 6;\n\t"
+        "mov.b64 b0, {%0, %1};\n\tmov.b64 b1, {l1, %1};\n\tmov.b64 b2, {l2, %1};\n\tmov.b64 b3, {l3, %1};\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a0], b0, %2, p;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a1], b1, %2, one;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a2], b2, %2, one;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a3], b3, %2, one;\n\t}\n"
+        ::"r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate_first), "n"(D_TMEM), "n"(A_TMEM)
+        : "memory");
+}
+// same with A from shared memory (descriptor advanced like B's)
+template <uint32_t D_TMEM>
+__device__ __forceinline__ void umma2_f16_ss_chunk_warp(uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                                        uint32_t accumulate_first) {
+    asm volatile(
+        "{\n\t.reg .pred p, q, one;\n\t.reg .b32 d, l1, l2, l3, m1, m2, m3;\n\t.reg .b64 a0, a1, a2, a3, b0, b1, b2, b3;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "setp.eq.b32 one, 0, 0;\n\t"
+        "mov.u32 d, %6;\n\t"
+        "add.u32 m1, %0, 2;\n\tadd.u32 m2, %0, 4;\n\tadd.u32 m3, %0, 6;\n\t"
+        "add.u32 l1, %2, 2;\n\tadd.u32 l2, %2, 4;\n\tadd.u32 l3, %2, 6;\n\t"
+        "mov.b64 a0, {%0, %1};\n\tmov.b64 a1, {m1, %1};\n\tmov.b64 a2, {m2, %1};\n\tmov.b64 a3, {m3, %1};\n\t"
+        "mov.b64 b0, {%2, %3};\n\tmov.b64 b1, {l1, %3};\n\tmov.b64 b2, {l2, %3};\n\tmov.b64 b3, {l3, %3};\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a0, b0, %4, p;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a1, b1, %4, one;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a2, b2, %4, one;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a3, b3, %4, one;\n\t}\n"
+        ::"r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate_first), "n"(D_TMEM)
+        : "memory");
+}
 // arrives on the mbarrier at this offset in BOTH CTAs of the pair when the issuing thread's MMAs have completed
 __device__ __forceinline__ void umma2_commit_warp(uint64_t* bar) {
     asm volatile(
