@@ -173,3 +173,22 @@ def test_forward_into_preallocated_outputs():
     assert res[0] is out[0] and torch.equal(out[0], mel) and torch.equal(out[1], post) and torch.equal(out[2], codes)
     with pytest.raises(RuntimeError):
         m(x, c_org, c_trg, out=(out[0][:2], out[1], out[2]))
+
+
+@pytest.mark.parametrize("B,T", [(300, 64), (130, 96), (97, 33)])
+def test_batches_beyond_one_recurrence_launch(B, T):
+    """B > 256 runs the recurrences as several co-resident launches (256 + 44 rows), B = 130 takes 64-wide tiles for lstm2 and
+    32-wide ones for lstm1, B = 97 is ragged in both: every row equals the same row computed in a small batch, and a sample
+    of rows matches the oracle."""
+    from oracle import autovc_oracle as O
+    m = model("bf16")
+    x, c_org, c_trg = synth_inputs(B, T, seed=B)
+    mel, post, codes = m(x.cuda(), c_org.cuda(), c_trg.cuda())
+    rows = [0, B // 2, 255 if B > 256 else B - 2, B - 1]
+    idx = torch.tensor(rows)
+    mel_s, post_s, codes_s = m(x[idx].cuda(), c_org[idx].cuda(), c_trg[idx].cuda())
+    assert float((post[idx.cuda()] - post_s).abs().max()) <= 1e-5
+    assert float((codes[idx.cuda()] - codes_s).abs().max()) <= 1e-5
+    ref_mel, ref_post, ref_codes = O.generator_forward(synth_state_dict(0), x[idx], c_org[idx], c_trg[idx])
+    assert float((post_s.cpu() - ref_post).abs().max()) <= BF16_POST_TOL
+    assert torch.isfinite(post).all()
