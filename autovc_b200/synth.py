@@ -136,3 +136,72 @@ def synth_speaker_encoder(seed: int = 5, n_partials: int = 8, n_frames: int = 16
         sd[n] = torch.from_numpy(rng.uniform(-1 / 16, 1 / 16, size=shp).astype(np.float32))
     parts = torch.from_numpy(rng.normal(size=(n_partials, n_frames, 40)).astype(np.float32))
     return sd, parts
+
+
+# ---- WaveRNN vocoder -------------------------------------------------------------------------------
+WAVERNN = dict(hop_length=275, rnn_dims=512, res_out_dims=128, feat_dims=80, fc_dims=512, bits=9, upsample_factors=(5, 5, 11),
+               compute_dims=128, pad=2, res_blocks=10, mode="MOL")                       # reference utils/hparams.py:92-107
+
+
+def synth_wavernn_state_dict(seed: int = 11, logit_gain: float = 1.0) -> Dict[str, torch.Tensor]:
+    """Seeded weights under the reference `WaveRNN` state-dict names (`autovc/wavernn/model.py:158-172`; the pretrained
+    blob is absent, `.MISSING_LARGE_BLOBS:1`).  PyTorch default magnitudes (U(-1/sqrt(fan_in), ..) for conv / linear /
+    GRU), BatchNorm statistics randomised so that folding is exercised, the box filters of the up-sampling convolutions
+    (`model.py:81-82`: filled with 1/k) perturbed so that a wrong tap order shows."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    sd: Dict[str, torch.Tensor] = {}
+
+    def uni(shape, fan_in, gain=1.0):
+        b = gain / math.sqrt(fan_in)
+        return torch.from_numpy(rng.uniform(-b, b, size=shape).astype(np.float32))
+
+    def bn(prefix, c):
+        sd[prefix + ".weight"] = torch.from_numpy(rng.uniform(0.5, 1.5, c).astype(np.float32))
+        sd[prefix + ".bias"] = torch.from_numpy((0.1 * rng.standard_normal(c)).astype(np.float32))
+        sd[prefix + ".running_mean"] = torch.from_numpy((0.1 * rng.standard_normal(c)).astype(np.float32))
+        sd[prefix + ".running_var"] = torch.from_numpy(rng.uniform(0.5, 1.5, c).astype(np.float32))
+        sd[prefix + ".num_batches_tracked"] = torch.tensor(1, dtype=torch.long)
+
+    cd, feat, ro = WAVERNN["compute_dims"], WAVERNN["feat_dims"], WAVERNN["res_out_dims"]
+    k = 2 * WAVERNN["pad"] + 1
+    sd["upsample.resnet.conv_in.weight"] = uni((cd, feat, k), feat * k)
+    bn("upsample.resnet.batch_norm", cd)
+    for i in range(WAVERNN["res_blocks"]):
+        p = f"upsample.resnet.layers.{i}"
+        sd[p + ".conv1.weight"] = uni((cd, cd, 1), cd)
+        sd[p + ".conv2.weight"] = uni((cd, cd, 1), cd)
+        bn(p + ".batch_norm1", cd)
+        bn(p + ".batch_norm2", cd)
+    sd["upsample.resnet.conv_out.weight"] = uni((ro, cd, 1), cd)
+    sd["upsample.resnet.conv_out.bias"] = uni((ro,), cd)
+    for i, s in enumerate(WAVERNN["upsample_factors"]):
+        ks = 2 * s + 1
+        w = (1.0 / ks) * (1.0 + 0.2 * rng.uniform(-1, 1, size=(1, 1, 1, ks)))
+        sd[f"upsample.up_layers.{2 * i + 1}.weight"] = torch.from_numpy(w.astype(np.float32))
+    R, aux, fc = WAVERNN["rnn_dims"], ro // 4, WAVERNN["fc_dims"]
+    sd["I.weight"] = uni((R, feat + aux + 1), feat + aux + 1)
+    sd["I.bias"] = uni((R,), feat + aux + 1)
+    for name, cin in (("rnn1", R), ("rnn2", R + aux)):
+        sd[f"{name}.weight_ih_l0"] = uni((3 * R, cin), R)
+        sd[f"{name}.weight_hh_l0"] = uni((3 * R, R), R)
+        sd[f"{name}.bias_ih_l0"] = uni((3 * R,), R)
+        sd[f"{name}.bias_hh_l0"] = uni((3 * R,), R)
+    sd["fc1.weight"] = uni((fc, R + aux), R + aux)
+    sd["fc1.bias"] = uni((fc,), R + aux)
+    sd["fc2.weight"] = uni((fc, fc + aux), fc + aux)
+    sd["fc2.bias"] = uni((fc,), fc + aux)
+    # the 30 mixture logits: means in about +-0.5, log-scales around -3 (a trained vocoder's range), so that the
+    # sample actually depends on the network instead of saturating the [-1, 1] clamp
+    sd["fc3.weight"] = uni((30, fc), fc, gain=4.0 * logit_gain)
+    b3 = uni((30,), fc)
+    b3[20:] -= 3.0
+    sd["fc3.bias"] = b3
+    sd["step"] = torch.zeros(1, dtype=torch.long)
+    return sd
+
+
+def synth_uniforms(n_steps: int, batch: int, seed: int = 21) -> np.ndarray:
+    """The random stream one `generate` consumes: per step and row, 10 uniforms for the mixture choice and one for the
+    logistic (`autovc/wavernn/distribution.py:106,117`: both `uniform_(1e-5, 1 - 1e-5)`).  float32 (n_steps, batch, 11)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    return rng.uniform(1e-5, 1.0 - 1e-5, size=(n_steps, batch, 11)).astype(np.float32)
