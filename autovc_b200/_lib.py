@@ -23,7 +23,9 @@ AVC_PREC_FP32 = 1
 EXPORTS = ["avc_abi_version", "avc_create", "avc_load_weights", "avc_workspace_bytes", "avc_forward", "avc_encode",
            "avc_last_launch_count", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error",
            "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_reduce",
-           "avc_mel_create", "avc_mel_num_frames", "avc_mel_filterbank", "avc_mel_forward", "avc_mel_last_error", "avc_mel_destroy"]
+           "avc_mel_create", "avc_mel_num_frames", "avc_mel_filterbank", "avc_mel_forward", "avc_mel_last_error", "avc_mel_destroy",
+           "avc_voc_create", "avc_voc_load_weights", "avc_voc_condition_workspace_bytes", "avc_voc_condition", "avc_voc_max_rows",
+           "avc_voc_generate_workspace_bytes", "avc_voc_generate", "avc_voc_last_launch_count", "avc_voc_last_error", "avc_voc_destroy"]
 
 
 class AvcDims(Structure):
@@ -95,6 +97,27 @@ def lib() -> ctypes.CDLL:
     L.avc_mel_last_error.restype = c_char_p
     L.avc_mel_destroy.argtypes = [c_void_p]
     L.avc_mel_destroy.restype = None
+    L.avc_voc_create.argtypes = [POINTER(c_void_p), c_int]
+    L.avc_voc_create.restype = c_int
+    L.avc_voc_load_weights.argtypes = [c_void_p, POINTER(AvcWeightDesc), c_int]
+    L.avc_voc_load_weights.restype = c_int
+    L.avc_voc_condition_workspace_bytes.argtypes = [c_void_p, c_int, c_int]
+    L.avc_voc_condition_workspace_bytes.restype = c_size_t
+    L.avc_voc_condition.argtypes = [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
+    L.avc_voc_condition.restype = c_int
+    L.avc_voc_max_rows.argtypes = []
+    L.avc_voc_max_rows.restype = c_int
+    L.avc_voc_generate_workspace_bytes.argtypes = [c_void_p, c_int, c_int]
+    L.avc_voc_generate_workspace_bytes.restype = c_size_t
+    L.avc_voc_generate.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p,
+                                   ctypes.c_uint64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
+    L.avc_voc_generate.restype = c_int
+    L.avc_voc_last_launch_count.argtypes = [c_void_p]
+    L.avc_voc_last_launch_count.restype = c_int64
+    L.avc_voc_last_error.argtypes = [c_void_p]
+    L.avc_voc_last_error.restype = c_char_p
+    L.avc_voc_destroy.argtypes = [c_void_p]
+    L.avc_voc_destroy.restype = None
     L.avc_destroy.argtypes = [c_void_p]
     L.avc_destroy.restype = None
     L.avc_last_error.argtypes = [c_void_p]

@@ -564,7 +564,7 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
 // ---------------------------------------------------------------------------------------------
 extern "C" {
 
-int avc_abi_version(void) { return 3; }
+int avc_abi_version(void) { return 4; }
 
 int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision) {
     if (!out || !dims) return fail(nullptr, AVC_ERR_INVALID_ARG, "null out/dims");

@@ -186,11 +186,49 @@ const char* avc_mel_last_error(avc_mel_handle h);   /* h may be NULL: error of t
 void avc_mel_destroy(avc_mel_handle h);
 
 
+/* ---- WaveRNN vocoder: mel -> waveform samples -------------------------------------------------------
+ * Replaces the device work of WaveRNN.generate (reference autovc/wavernn/model.py:214-329, eval mode, mode 'MOL'):
+ * UpsampleNetwork.forward (:85-92 with MelResNet :33-52 and Stretch2d :55-64), the per-sample loop (:265-310: I, two GRU
+ * cells, fc1-fc3) and sample_from_discretized_mix_logistic (autovc/wavernn/distribution.py:87-123).  Folding and the
+ * cross-fade (:358-456) are index arithmetic / float64 numpy on the host in the reference and stay there
+ * (autovc_b200/vocoder.py); the fold itself is expressed here as row windows.  Independent of avc_handle.
+ * Weights: the reference module's state dict under its own names ("I.weight" [512,113], "rnn1.weight_ih_l0" [1536,512],
+ * "rnn2.weight_ih_l0" [1536,544], "fc1.weight" [512,544], "fc3.weight" [30,512], "upsample.resnet.conv_in.weight"
+ * [128,80,5], "upsample.resnet.layers.<i>.conv1.weight", "...batch_norm1.running_mean", "upsample.up_layers.1.weight"
+ * [1,1,1,11] ...), hyper-parameters fixed to utils/hparams.py:92-107.  bf16 operands, fp32 accumulation and state. */
+typedef struct avc_voc_ctx* avc_voc_handle;
+
+int avc_voc_create(avc_voc_handle* out, int device);      /* device < 0: host-only handle (weights can be checked, nothing runs) */
+int avc_voc_load_weights(avc_voc_handle h, const avc_weight_desc* table, int n);
+
+/* UpsampleNetwork on U utterances of T mel frames: mel DEVICE [U][80][T] float32 (un-padded: the `pad` = 2 zero frames of
+ * generate, model.py:252, are applied inside) -> m_up [U][T*275][80] (the up-sampled mels, transposed as :92 returns them)
+ * and aux [U][T][128] at FRAME rate (the reference's aux is this repeated 275 times along time, Stretch2d :74). */
+size_t avc_voc_condition_workspace_bytes(avc_voc_handle h, int U, int T);
+int avc_voc_condition(avc_voc_handle h, const float* mel, int U, int T, float* m_up, float* aux, void* workspace, void* stream);
+
+/* The sample loop on `rows` independent rows of `steps` samples.  Row i reads the conditioning of utterance row_utt[i] from
+ * position row_start[i] on and zeros past the end of the utterance (pad_tensor 'after' + fold_with_overlap); the
+ * unbatched generate is one row with start 0.  row_utt / row_start: DEVICE int32 [rows].  rows <= avc_voc_max_rows().
+ *   uniforms : DEVICE [steps][rows][11] float32 in (0,1): 10 for the mixture choice, 1 for the logistic
+ *              (distribution.py:106,117), or NULL: a Philox4x32-10 stream keyed by `seed`, step and row
+ *   forced_x : NULL, or DEVICE [steps][rows]: fed back instead of the drawn sample (teacher forcing, for parity tests)
+ *   samples  : DEVICE out [rows][steps] float32 in [-1, 1]
+ *   logits   : NULL, or DEVICE out [steps][rows][30] (the fc3 output of every step, for parity tests) */
+int avc_voc_max_rows(void);
+size_t avc_voc_generate_workspace_bytes(avc_voc_handle h, int rows, int steps);
+int avc_voc_generate(avc_voc_handle h, const float* m_up, const float* aux, int U, int T, const int32_t* row_utt, const int32_t* row_start,
+                     int rows, int steps, const float* uniforms, uint64_t seed, const float* forced_x, float* samples, float* logits,
+                     void* workspace, void* stream);
+int64_t avc_voc_last_launch_count(avc_voc_handle h);
+const char* avc_voc_last_error(avc_voc_handle h);   /* h may be NULL: error of the last failed avc_voc_create on this thread */
+void avc_voc_destroy(avc_voc_handle h);
+
 /* Last error message of this handle (or of the failed avc_create when h == NULL). Never NULL. */
 const char* avc_last_error(avc_handle h);
 
 /* ABI version; bumped on any signature change. */
-int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end */
+int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder */
 
 #ifdef __cplusplus
 }
