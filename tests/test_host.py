@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     lib = ctypes.CDLL(built_lib)
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/autovc_b200.h but not exported"
-    assert lib.avc_abi_version() == 3
+    assert lib.avc_abi_version() == 4
 
 
 def test_state_dict_contract():
@@ -108,3 +108,38 @@ def test_overlap_average_matches_oracle():
     x = torch.randn(4, 80, 64)
     assert torch.allclose(autovc_b200.overlap_average(x, 0.5), O.overlap_average(x, 0.5))
     assert autovc_b200.overlap_average(x, 0.25).shape == (80, 64 + 3 * 48)
+
+
+def test_vocoder_state_dict_contract_and_host_packing(built_lib):
+    """The vocoder module carries the reference's state-dict names (strict load of the seeded dict) and the C ABI folds
+    and packs them on a host-only handle (no GPU): a missing entry is an error that names it."""
+    from autovc_b200 import _lib as L
+    from autovc_b200.synth import synth_wavernn_state_dict
+    from autovc_b200.vocoder import WaveRNN, fold_params
+    sd = synth_wavernn_state_dict(11)
+    m = WaveRNN(device="cpu")
+    res = m.load_state_dict(sd, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    assert m.state_dict()["upsample.up_layers.5.weight"].shape == (1, 1, 1, 23)
+    h = ctypes.c_void_p()
+    assert L.lib().avc_voc_create(ctypes.byref(h), -1) == L.AVC_OK
+    keep = {k: v.float().contiguous() for k, v in sd.items() if k != "step" and not k.endswith("num_batches_tracked")}
+
+    def load(d):
+        table = (L.AvcWeightDesc * len(d))()
+        for i, (k, v) in enumerate(d.items()):
+            table[i] = L.AvcWeightDesc(k.encode(), ctypes.cast(v.data_ptr(), ctypes.POINTER(ctypes.c_float)), v.numel())
+        return L.lib().avc_voc_load_weights(h, table, len(d))
+
+    assert load(keep) == L.AVC_OK
+    bad = dict(keep)
+    del bad["rnn2.weight_hh_l0"]
+    assert load(bad) == L.AVC_ERR_MISSING_WEIGHT and b"rnn2.weight_hh_l0" in L.lib().avc_voc_last_error(h)
+    bad = dict(keep)
+    bad["I.weight"] = bad["I.weight"][:, :112].contiguous()
+    assert load(bad) == L.AVC_ERR_MISSING_WEIGHT and b"I.weight" in L.lib().avc_voc_last_error(h)
+    L.lib().avc_voc_destroy(h)
+    # the fold arithmetic of generate (model.py:381-391)
+    assert fold_params(35200, 11000, 550) == (3, 0) and fold_params(6050, 2950, 50) == (2, 0) and fold_params(6600, 1500, 100) == (5, 1600)
+    with pytest.raises(RuntimeError):
+        WaveRNN(device="cpu").condition(torch.zeros(1, 80, 30))
