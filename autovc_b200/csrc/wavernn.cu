@@ -92,13 +92,15 @@ struct VocArgs {
     uint8_t* h1;                    // [2][tiles][ACT_BYTES]   (double-buffered by step parity)
     uint8_t* h2;                    // [2][tiles][ACT_BYTES]
     uint8_t* x1; uint8_t* x2; uint8_t* y1; uint8_t* y2;       // [tiles][ACT_BYTES]
-    unsigned int* counter;          // grid-phase counter, zero at launch
+    unsigned int* counter;          // per-tile phase counters (128 bytes apart), zero at launch
     const float* uniforms;          // [L][R][11] or nullptr (then Philox with `seed`)
     unsigned long long seed;
     const float* forced;            // [L][R] or nullptr: fed back instead of the sample (teacher forcing)
     float* samples;                 // [R][L]
     float* logits;                  // [L][R][30] or nullptr
     uint32_t idesc32, idesc16;
+    int stages;                     // ring stages in use (<= STAGES; AVC_VOC_STAGES, for experiments)
+    int cs;                         // cluster size: the CTAs of a cluster fetch each activation block once and multicast it
 };
 
 __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
@@ -146,7 +148,8 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
     constexpr unsigned int ARRIVALS = 4 * VCTAS;        // one increment per epilogue warp and CTA per phase
 
     if (warp == 0 && lane == 0) {
-        for (int i = 0; i < STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
+        // a ring stage is refilled for the whole cluster, so it is free only when all cs CTAs have consumed it
+        for (int i = 0; i < STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], (uint32_t)a.cs); }
         ptx::mbar_init(wfull, 1);
         for (int m = 0; m < MAX_TILES; ++m) { ptx::mbar_init(&accA[m], 1); ptx::mbar_init(&accX[m], 1); }
         ptx::fence_barrier_init();
@@ -155,56 +158,72 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
     if (threadIdx.x >= 128 && threadIdx.x < 128 + NPARAM) sP[threadIdx.x - 128] = a.params[(size_t)cta * NPARAM + threadIdx.x - 128];
     ptx::tc_fence_before();
     __syncthreads();
+    if (a.cs > 1) ptx::cluster_sync();      // peers' barriers are initialised before anyone multicasts / commits into them
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const uint32_t crank = a.cs > 1 ? ptx::cluster_ctarank() : 0u;
+    const uint16_t cmask = (uint16_t)((1u << a.cs) - 1u);
 
     if (warp == 0) {
-        // ===================== producer =====================
+        // ===================== producer: the whole warp, lane i brings block i of a group =====================
+        // (the issue of one bulk copy costs its thread a few hundred cycles whatever its size; eight lanes issue the eight
+        // blocks of an activation side by side)
         if (lane == 0) {
             constexpr int WCH = W_BYTES / 6;                    // 19,456 B per copy
             ptx::mbar_expect_tx(wfull, (uint32_t)W_BYTES);
             for (int i = 0; i < 6; ++i) ptx::bulk_load(sW + i * WCH, a.wpack + (size_t)cta * W_BYTES + i * WCH, WCH, wfull);
-            int stage = 0; uint32_t phase = 0;
-            auto load = [&](const uint8_t* src, int nblk) {
-                for (int i = 0; i < nblk; ++i) {
-                    ptx::mbar_wait(&empty[stage], phase ^ 1);
-                    ptx::mbar_expect_tx(&full[stage], (uint32_t)BLK);
-                    ptx::bulk_load(sRing + stage * BLK, src + (size_t)i * BLK, (uint32_t)BLK, &full[stage]);
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        int stage = 0; uint32_t phase = 0, seq = 0;
+        auto load = [&](const uint8_t* src, int nblk) {
+            // sub-groups of at most 4 (< STAGES) blocks with a warp sync after each: every earlier use of a stage has been
+            // ISSUED before a lane waits for it to be consumed, so the parity it waits on is never two phases away
+            for (int b0 = 0; b0 < nblk; b0 += min(4, a.stages - 1)) {
+                const int n = min(min(4, a.stages - 1), nblk - b0);
+                if (lane < n) {
+                    const int pos = stage + lane;
+                    const int st = pos % a.stages;
+                    const uint32_t ph = phase ^ (uint32_t)(pos / a.stages);
+                    ptx::mbar_wait(&empty[st], ph ^ 1);
+                    ptx::mbar_expect_tx(&full[st], (uint32_t)BLK);
+                    if (a.cs == 1) ptx::bulk_load(sRing + st * BLK, src + (size_t)(b0 + lane) * BLK, (uint32_t)BLK, &full[st]);
+                    else if ((seq + (uint32_t)lane) % (uint32_t)a.cs == crank)      // one L2 read serves the cluster
+                        ptx::bulk_load_mc(sRing + st * BLK, src + (size_t)(b0 + lane) * BLK, (uint32_t)BLK, &full[st], cmask);
                 }
-            };
-            auto wait_grid = [&](unsigned int k) {              // all CTAs have finished k phases
-                const unsigned int target = ARRIVALS * k;
-                for (uint32_t spin = 0; spin < (1u << 27); ++spin)
-                    if (ld_acquire_u32(a.counter) >= target) {
-                        asm volatile("fence.proxy.async.global;" ::: "memory");   // their generic-proxy stores -> our bulk reads
-                        return;
-                    }
-                printf("autovc_b200: vocoder phase counter timed out (cta %d, want %u, have %u)\n", cta, target, ld_acquire_u32(a.counter));
-                __trap();
-            };
-            for (int t = 0; t < a.L; ++t) {
-                const int prev = (t + 1) & 1;                                   // buffer holding h(t-1); zero-filled for t = 0
-                const uint8_t* cond_t = a.cond + (size_t)t * MT * COND_BLKS * BLK;
-                for (int m = 0; m < MT; ++m) {                                  // A: h1(t-1) | cond 0,1
-                    load(a.h1 + ((size_t)prev * MT + m) * ACT_BYTES, NKB);
-                    load(cond_t + (size_t)(m * COND_BLKS) * BLK, 2);
-                }
-                for (int m = 0; m < MT; ++m) {                                  // B, independent part: h2(t-1) | aux2
-                    load(a.h2 + ((size_t)prev * MT + m) * ACT_BYTES, NKB);
-                    load(cond_t + (size_t)(m * COND_BLKS + 2) * BLK, 1);
-                }
-                wait_grid(4u * t + 1);
-                for (int m = 0; m < MT; ++m) load(a.x1 + (size_t)m * ACT_BYTES, NKB);
-                for (int m = 0; m < MT; ++m) load(cond_t + (size_t)(m * COND_BLKS + 3) * BLK, 1);       // C
-                wait_grid(4u * t + 2);
-                for (int m = 0; m < MT; ++m) load(a.x2 + (size_t)m * ACT_BYTES, NKB);
-                for (int m = 0; m < MT; ++m) load(cond_t + (size_t)(m * COND_BLKS + 4) * BLK, 1);       // D
-                wait_grid(4u * t + 3);
-                for (int m = 0; m < MT; ++m) load(a.y1 + (size_t)m * ACT_BYTES, NKB);
-                wait_grid(4u * t + 4);                                                                  // E
-                for (int m = 0; m < MT; ++m) load(a.y2 + (size_t)m * ACT_BYTES, NKB);
+                seq += (uint32_t)n;
+                __syncwarp();
+                const int pos = stage + n;
+                phase ^= (uint32_t)(pos / a.stages);
+                stage = pos % a.stages;
             }
+        };
+        auto wait_grid = [&](int m, unsigned int k) {           // all CTAs have finished k phases of tile m
+            const unsigned int target = ARRIVALS * k;
+            const unsigned int* ctr = a.counter + m * 32;
+            for (uint32_t spin = 0; spin < (1u << 27); ++spin)
+                if (ld_acquire_u32(ctr) >= target) {
+                    asm volatile("fence.proxy.async.global;" ::: "memory");   // their generic-proxy stores -> our bulk reads
+                    return;
+                }
+            printf("autovc_b200: vocoder phase counter timed out (cta %d tile %d, want %u, have %u)\n", cta, m, target, ld_acquire_u32(ctr));
+            __trap();
+        };
+        for (int t = 0; t < a.L; ++t) {
+            const int prev = (t + 1) & 1;                                   // buffer holding h(t-1); zero-filled for t = 0
+            const uint8_t* cond_t = a.cond + (size_t)t * MT * COND_BLKS * BLK;
+            for (int m = 0; m < MT; ++m) {                                  // A: h1(t-1) | cond 0,1
+                load(a.h1 + ((size_t)prev * MT + m) * ACT_BYTES, NKB);
+                load(cond_t + (size_t)(m * COND_BLKS) * BLK, 2);
+            }
+            for (int m = 0; m < MT; ++m) {                                  // B, independent part: h2(t-1) | aux2
+                load(a.h2 + ((size_t)prev * MT + m) * ACT_BYTES, NKB);
+                load(cond_t + (size_t)(m * COND_BLKS + 2) * BLK, 1);
+            }
+            for (int m = 0; m < MT; ++m) { wait_grid(m, 4u * t + 1); load(a.x1 + (size_t)m * ACT_BYTES, NKB); }
+            for (int m = 0; m < MT; ++m) load(cond_t + (size_t)(m * COND_BLKS + 3) * BLK, 1);       // C
+            for (int m = 0; m < MT; ++m) { wait_grid(m, 4u * t + 2); load(a.x2 + (size_t)m * ACT_BYTES, NKB); }
+            for (int m = 0; m < MT; ++m) load(cond_t + (size_t)(m * COND_BLKS + 4) * BLK, 1);       // D
+            for (int m = 0; m < MT; ++m) { wait_grid(m, 4u * t + 3); load(a.y1 + (size_t)m * ACT_BYTES, NKB); }
+            for (int m = 0; m < MT; ++m) { wait_grid(m, 4u * t + 4); load(a.y2 + (size_t)m * ACT_BYTES, NKB); }   // E
         }
     } else if (warp == 1) {
         // ===================== MMA issue =====================
@@ -221,8 +240,9 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
 #pragma unroll
                     for (int k = 0; k < KB / 16; ++k)
                         ptx::umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (fresh && i == 0 && k == 0) ? 0u : 1u);
-                    ptx::umma_commit(&empty[stage]);
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (a.cs == 1) ptx::umma_commit(&empty[stage]);
+                    else ptx::umma_commit_mc(&empty[stage], cmask);
+                    if (++stage == a.stages) { stage = 0; phase ^= 1; }
                 }
             };
             for (int t = 0; t < a.L; ++t) {
@@ -270,10 +290,10 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
             __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
             return make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
         };
-        auto publish = [&]() {
+        auto publish = [&](int m) {                 // this warp's rows of tile m are stored: one arrival on the tile's counter
             asm volatile("fence.proxy.async.global;" ::: "memory");
             __syncwarp();
-            if (lane == 0) red_release_add_u32(a.counter, 1u);
+            if (lane == 0) red_release_add_u32(a.counter + m * 32, 1u);
         };
         for (int t = 0; t < a.L; ++t) {
             const int cur = t & 1;
@@ -322,9 +342,9 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
                 }
                 *reinterpret_cast<uint2*>(a.h1 + ((size_t)cur * MT + m) * ACT_BYTES + act_off) = pack4(hv);
                 *reinterpret_cast<uint2*>(a.x1 + (size_t)m * ACT_BYTES + act_off) = pack4(x1[m]);
+                publish(m);
             }
             parA ^= 1;
-            publish();
             // ---- B: GRU 2 ----
 #pragma unroll
             for (int m = 0; m < MT; ++m) {
@@ -345,9 +365,9 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
                 }
                 *reinterpret_cast<uint2*>(a.h2 + ((size_t)cur * MT + m) * ACT_BYTES + act_off) = pack4(hv);
                 *reinterpret_cast<uint2*>(a.x2 + (size_t)m * ACT_BYTES + act_off) = pack4(x1[m]);
+                publish(m);
             }
             parX ^= 1;
-            publish();
             // ---- C, D: fc1, fc2 ----
 #pragma unroll
             for (int ph = 0; ph < 2; ++ph) {
@@ -362,9 +382,9 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
 #pragma unroll
                     for (int j = 0; j < VU; ++j) y[j] = fmaxf(__uint_as_float(d0[j]) + sP[(ph ? P_BD : P_BC) + j], 0.0f);
                     *reinterpret_cast<uint2*>((ph ? a.y2 : a.y1) + (size_t)m * ACT_BYTES + act_off) = pack4(y);
+                    publish(m);
                 }
                 parX ^= 1;
-                publish();
             }
             // ---- E: fc3 + mixture-of-logistics sample (distribution.py:87-123), identical in every CTA ----
 #pragma unroll
@@ -404,6 +424,7 @@ __global__ void __launch_bounds__(256, 1) voc_generate_kernel(const VocArgs a) {
 
     ptx::tc_fence_before();
     __syncthreads();
+    if (a.cs > 1) ptx::cluster_sync();      // no CTA may exit while peers can still multicast / commit into it
     if (warp == 1) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
@@ -584,6 +605,7 @@ struct avc_voc_ctx {
     bool loaded = false;
     uint8_t* d_wpack = nullptr; float* d_params = nullptr;
     float *d_w_in = nullptr, *d_b_in = nullptr, *d_w_res = nullptr, *d_b_res = nullptr, *d_w_out = nullptr, *d_b_out = nullptr, *d_up = nullptr;
+    int cs = 1;                 // cluster size of the loop kernel (multicast of the activation blocks)
     int64_t launches = 0;
     std::string err;
 };
@@ -644,6 +666,20 @@ int avc_voc_create(avc_voc_handle* out, int device) {
         cudaFuncSetAttribute(voc_generate_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         cudaFuncSetAttribute(voc_generate_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         cudaFuncSetAttribute(voc_generate_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        // largest cluster (<= 8, or AVC_VOC_CLUSTER) for which all 128 CTAs are still co-resident
+        const char* env = getenv("AVC_VOC_CLUSTER");
+        for (int c = env ? atoi(env) : 8; c >= 2; c >>= 1) {
+            if (c > 8 || (c & (c - 1))) continue;
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(VCTAS); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = SMEM_BYTES;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = (unsigned)c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            int ncl = 0;
+            if (cudaOccupancyMaxActiveClusters(&ncl, voc_generate_kernel<1>, &cfg) == cudaSuccess && ncl * c >= VCTAS) { h->cs = c; break; }
+        }
+        cudaGetLastError();
     }
     *out = h;
     return AVC_OK;
@@ -856,14 +892,18 @@ int avc_voc_generate(avc_voc_handle h, const float* m_up, const float* aux, int 
     a.idesc16 = ptx::umma_idesc_f16(1, TILE, 16);
     void* kargs[] = {&a};
     const void* fn = tiles == 1 ? (const void*)voc_generate_kernel<1> : tiles == 2 ? (const void*)voc_generate_kernel<2> : (const void*)voc_generate_kernel<4>;
-    cudaError_t e;
-    if (getenv("AVC_VOC_NOCOOP")) {            // profilers that cannot replay cooperative launches; co-residency then rests on an idle GPU
-        cudaLaunchConfig_t cfg{};
-        cfg.gridDim = dim3(VCTAS); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = s;
-        e = cudaLaunchKernelExC(&cfg, fn, kargs);
-    } else {
-        e = cudaLaunchCooperativeKernel(fn, dim3(VCTAS), dim3(256), kargs, SMEM_BYTES, s);
-    }
+    a.cs = h->cs;
+    a.stages = getenv("AVC_VOC_STAGES") ? std::max(2, std::min(STAGES, atoi(getenv("AVC_VOC_STAGES")))) : STAGES;
+    // cooperative launch: CTAs wait on one another's output, so co-residency must be guaranteed.  AVC_VOC_NOCOOP drops the
+    // attribute for profilers that cannot replay cooperative cluster launches (the grid is sized to be co-resident anyway).
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(VCTAS); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = s;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)h->cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
+    cfg.attrs = at; cfg.numAttrs = getenv("AVC_VOC_NOCOOP") ? 1 : 2;
+    cudaError_t e = cudaLaunchKernelExC(&cfg, fn, kargs);
     h->launches = 3;
     if (e != cudaSuccess) return voc_fail(h, AVC_ERR_CUDA, "vocoder loop launch failed: %s", cudaGetErrorString(e));
     return AVC_OK;

@@ -3,7 +3,8 @@ vectors produced by the unmodified reference module.
 
 Tolerances.  The device path computes with bf16 operands (weights and the exchanged activations) and fp32 accumulation /
 state; the oracle is float32 throughout.  Element-wise bounds are stated on a TEACHER-FORCED run (the oracle's samples fed
-back), where they mean something: |logits| error <= 2e-2 and |sample| error <= 2e-2 (measured: 3e-3 / 2e-3).  A free run
+back), where they mean something: |logits| error <= 2e-2 and |sample| error <= 2e-2 (measured: 3e-3 / 2e-3) wherever the
+mixture choice is not a near-tie.  A free run
 feeds its own samples back through 2 GRUs for thousands of steps; its error is bounded statistically (median, tail),
 and exactly for the first steps.  The conditioning network is fp32: <= 1e-5.
 """
@@ -64,14 +65,21 @@ def test_forced_run_matches_oracle(voc, sd):
     mels_f, aux_f, starts = _folded(sd, mel, target, overlap)
     B = len(starts)
     # the last fold runs off the end of the conditioning after 200 steps (zeros: pad_tensor 'after')
-    off = 1300
+    off = 0
     U = synth_uniforms(n, B, 21)
     ref, lg_ref = wo.generate_rows(sd, mels_f[:, off:off + n], aux_f[:, off:off + n], U, return_logits=True)
     assert not mels_f[-1, off + n - 1].any() and mels_f[-1, off].any()
     m_up, aux = voc.condition(torch.from_numpy(mel).cuda())
     s, lg = voc.sample_rows(m_up, aux, [0] * B, [st + off for st in starts], n, uniforms=U, forced_x=ref.T.copy(), return_logits=True)
     assert np.abs(lg.cpu().numpy() - lg_ref).max() <= 2e-2
-    assert np.abs(s.cpu().numpy() - ref).max() <= 2e-2
+    # the sample is continuous in the logits except for the mixture choice (an argmax over Gumbel-perturbed logits): where
+    # the oracle's two best candidates are closer than twice the logits bound the choice may legitimately flip
+    pert = lg_ref[:, :, :10] - np.log(-np.log(U[:, :, :10]))
+    top2 = np.sort(pert, axis=2)[:, :, -2:]
+    near_tie = ((top2[:, :, 1] - top2[:, :, 0]) < 4e-2).T            # (rows, steps)
+    err = np.abs(s.cpu().numpy() - ref)
+    assert near_tie.mean() < 0.03
+    assert err[~near_tie].max() <= 2e-2
 
 
 @pytest.mark.parametrize("name", ["wavernn_t24_folded", "wavernn_t22_exactfold", "wavernn_t22_single"])
