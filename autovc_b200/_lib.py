@@ -20,7 +20,7 @@ AVC_ERR_UNSUPPORTED = -7
 AVC_PREC_BF16 = 0
 AVC_PREC_FP32 = 1
 
-EXPORTS = ["avc_abi_version", "avc_create", "avc_load_weights", "avc_workspace_bytes", "avc_forward", "avc_encode",
+EXPORTS = ["avc_abi_version", "avc_create", "avc_load_weights", "avc_workspace_bytes", "avc_forward", "avc_encode", "avc_forward_bn_train",
            "avc_last_launch_count", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error",
            "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_reduce",
            "avc_mel_create", "avc_mel_num_frames", "avc_mel_filterbank", "avc_mel_forward", "avc_mel_last_error", "avc_mel_destroy",
@@ -66,6 +66,9 @@ def lib() -> ctypes.CDLL:
     L.avc_forward.restype = c_int
     L.avc_encode.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]
     L.avc_encode.restype = c_int
+    L.avc_forward_bn_train.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_size_t, c_void_p]
+    L.avc_forward_bn_train.restype = c_int
     L.avc_last_launch_count.argtypes = [c_void_p]
     L.avc_last_launch_count.restype = c_int64
     L.avc_set_profiling.argtypes = [c_void_p, c_int]

@@ -40,8 +40,15 @@ enum LayerId {
     L_GEN_COUNT,
     // d-vector speaker encoder (reference autovc/speaker_encoder/model.py:48-58): LSTM(40,256,3) + Linear(256,256)
     L_SE_L0_IH = L_GEN_COUNT, L_SE_L0_HH, L_SE_L1_IH, L_SE_L1_HH, L_SE_L2_IH, L_SE_L2_HH, L_SE_LINEAR,
-    L_COUNT
+    // the 11 convolutions again WITHOUT the BatchNorm folded in, for the train-mode (batch statistics) forward
+    L_RAW_CONV0, L_RAW_COUNT_END = L_RAW_CONV0 + 11,
+    L_COUNT = L_RAW_COUNT_END
 };
+
+constexpr int N_BN = 11;   // BatchNorm layers in path order: encoder 0-2, decoder 0-2, postnet 0-4
+constexpr int BN_MAX_CH = 512;
+const int kBnFolded[N_BN] = {L_ENC_CONV0, L_ENC_CONV1, L_ENC_CONV2, L_DEC_CONV0, L_DEC_CONV1, L_DEC_CONV2,
+                             L_POST_CONV0, L_POST_CONV1, L_POST_CONV2, L_POST_CONV3, L_POST_CONV4};
 
 constexpr int SE_MELS = 40, SE_H = 256, SE_LAYERS = 3, SE_EMB = 256;   // reference utils/hparams.py:60-63, model.py:48-58
 
@@ -54,6 +61,8 @@ const char* kLayerNames[L_COUNT] = {
     "dec.linear",
     "post.conv0", "post.conv1", "post.conv2", "post.conv3", "post.conv4",
     "se.lstm.l0.ih", "se.lstm.l0.hh", "se.lstm.l1.ih", "se.lstm.l1.hh", "se.lstm.l2.ih", "se.lstm.l2.hh", "se.linear",
+    "raw.enc.conv0", "raw.enc.conv1", "raw.enc.conv2", "raw.dec.conv0", "raw.dec.conv1", "raw.dec.conv2",
+    "raw.post.conv0", "raw.post.conv1", "raw.post.conv2", "raw.post.conv3", "raw.post.conv4",
 };
 
 struct Workspace {
@@ -62,6 +71,7 @@ struct Workspace {
     char* Dm; float* Gd1; char* H1; float* G2; char* H2a; char* H2b; char* melc;
     unsigned int* ready; size_t ready_bytes;
     char* Yb;    // recurrent operand-tile copy of the running LSTM layer's output (tc_lstm.cu)
+    double* bn_partial; float* bn_ss;   // train-mode BatchNorm scratch (batchnorm.cu); the fp32 conv rows reuse G2
     size_t total;
 };
 
@@ -79,6 +89,8 @@ struct avc_ctx {
     std::string err = "";
     std::map<std::string, std::vector<float>> raw;
     Layer layers[L_COUNT];
+    float* bn_gamma_dev[N_BN] = {};   // BatchNorm weight / bias of the 11 conv blocks (train-mode forward)
+    float* bn_beta_dev[N_BN] = {};
     int64_t launches = 0;
     // tensor-core plan cache (valid for one (B,T,workspace) triple)
     std::vector<TcGemmPlan*> plans;
@@ -88,7 +100,7 @@ struct avc_ctx {
     bool simt_lstm = false;    // AVC_SIMT_LSTM=1: debugging aid, per-step CUDA-core recurrences in the bf16 mode
     int plan_B = 0, plan_T = 0;
     void* plan_ws = nullptr;
-    int plan_mode = 0;         // 0 forward, 1 encode only, 2 speaker encoder
+    int plan_mode = 0;         // 0 forward, 1 encode only, 2 speaker encoder, 3 / 4 forward / encode with batch-statistics BatchNorm
     // optional per-phase timing (avc_set_profiling): events at phase boundaries of the last run
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;
@@ -131,7 +143,7 @@ const std::vector<float>* find_raw(avc_ctx* h, const std::string& name, int64_t 
 
 // Conv1d(k=5) + eval BatchNorm -> packed [Cout][5*Cp], k = tap*Cp + ci, and folded bias.
 // reference net_layers.py:39-49 (conv), encoder.py:46 (BatchNorm1d, eps 1e-5).
-bool pack_conv(avc_ctx* h, Layer& L, const std::string& prefix, int cin, int cout) {
+bool pack_conv(avc_ctx* h, Layer& L, const std::string& prefix, int cin, int cout, bool fold = true) {
     const auto* w = find_raw(h, prefix + ".0.conv.weight", (int64_t)cout * cin * KTAPS);
     const auto* b = find_raw(h, prefix + ".0.conv.bias", cout);
     const auto* g = find_raw(h, prefix + ".1.weight", cout);
@@ -144,8 +156,8 @@ bool pack_conv(avc_ctx* h, Layer& L, const std::string& prefix, int cin, int cou
     L.w.assign((size_t)L.N * L.Kp, 0.0f);
     L.b.assign(L.N, 0.0f);
     for (int n = 0; n < cout; ++n) {
-        const double s = (double)(*g)[n] / std::sqrt((double)(*var)[n] + 1e-5);
-        L.b[n] = (float)(((double)(*b)[n] - (double)(*mu)[n]) * s + (double)(*be)[n]);
+        const double s = fold ? (double)(*g)[n] / std::sqrt((double)(*var)[n] + 1e-5) : 1.0;
+        L.b[n] = fold ? (float)(((double)(*b)[n] - (double)(*mu)[n]) * s + (double)(*be)[n]) : (*b)[n];
         for (int ci = 0; ci < cin; ++ci)
             for (int tap = 0; tap < KTAPS; ++tap)
                 L.w[(size_t)n * L.Kp + tap * L.Cp + ci] = (float)((double)(*w)[((size_t)n * cin + ci) * KTAPS + tap] * s);
@@ -250,6 +262,8 @@ Workspace carve(const avc_ctx* h, char* base, int B, int T) {
     w.ready_bytes = (size_t)tc_lstm_ready_words(B, T) * 4;
     w.ready = (unsigned int*)take(w.ready_bytes);
     w.Yb = take(tc_lstm_tile_bytes(B, T, hmax));
+    w.bn_partial = (double*)take((size_t)bn_chunks((int)M) * 2 * BN_MAX_CH * sizeof(double));
+    w.bn_ss = (float*)take((size_t)2 * BN_MAX_CH * sizeof(float));
     w.total = off;
     return w;
 }
@@ -310,6 +324,29 @@ struct Runner {
             check(launch_simt_gemm(p, s), L.name.c_str());
         }
         h->launches++;
+    }
+
+    // conv block `bn` (0..10): eval mode = one GEMM with the folded weights; train mode (bn_train) = GEMM with the unfolded
+    // weights -> fp32 rows -> batch statistics -> normalise + activation (batchnorm.cu).  reference encoder.py:69-70 etc.
+    bool bn_train = false;
+    float* bn_stats = nullptr;   // caller's [N_BN][2][BN_MAX_CH] (mean, biased var) or nullptr
+    void conv_bn(int bn, const void* A, int a_type, int lda, int M, int Tutt, int act, void* out, int out_type, int ldo,
+                 float* out_t = nullptr, const float* res_t = nullptr) {
+        if (!bn_train) { gemm(kBnFolded[bn], A, a_type, lda, M, Tutt, act, out, out_type, ldo, out_t, res_t); return; }
+        const Layer& L = h->layers[L_RAW_CONV0 + bn];
+        float* Z = wsp->G2;
+        gemm(L_RAW_CONV0 + bn, A, a_type, lda, M, Tutt, ACT_NONE, Z, DT_F32, L.N);
+        if (!ok()) return;
+        BnTrainParams q{};
+        q.Z = Z; q.M = M; q.N = L.N; q.T = Tutt;
+        q.gamma = h->bn_gamma_dev[bn]; q.beta = h->bn_beta_dev[bn]; q.eps = 1e-5f;
+        q.partial = wsp->bn_partial; q.scale_shift = wsp->bn_ss;
+        q.stat_mean = bn_stats ? bn_stats + (size_t)bn * 2 * BN_MAX_CH : nullptr;
+        q.stat_var = bn_stats ? bn_stats + (size_t)bn * 2 * BN_MAX_CH + BN_MAX_CH : nullptr;
+        q.act = act; q.out = out; q.out_type = out_type; q.out_t = out_t; q.res_t = res_t;
+        int n = 0;
+        check(launch_bn_train(q, s, &n), "train-mode BatchNorm");
+        h->launches += n;
     }
 
     // Full-sequence LSTM layer from a hoisted input projection Gx.
@@ -379,7 +416,8 @@ struct Runner {
 };
 
 int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int B, int T, float* mel, float* mel_post,
-        float* codes, void* workspace, size_t workspace_bytes, void* stream, bool encode_only) {
+        float* codes, void* workspace, size_t workspace_bytes, void* stream, bool encode_only, bool bn_train = false,
+        float* bn_stats = nullptr) {
     if (!h) return AVC_ERR_INVALID_ARG;
     if (h->device < 0) return fail(h, AVC_ERR_INVALID_ARG, "host-only context (device=-1) cannot run");
     if (!h->loaded) return fail(h, AVC_ERR_NOT_LOADED, "avc_load_weights has not completed");
@@ -395,11 +433,13 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
 
     Runner r{h, (cudaStream_t)stream, B, T};
     r.wsp = &w;
+    r.bn_train = bn_train; r.bn_stats = bn_stats;
+    const int mode = (encode_only ? 1 : 0) + (bn_train ? 3 : 0);
     h->launches = 0;
     for (auto ev : h->prof_events) cudaEventDestroy(ev);
     h->prof_events.clear(); h->prof_cats.clear();
     if (r.use_tc()) {
-        const bool hit = h->plan_ws == workspace && h->plan_B == B && h->plan_T == T && h->plan_mode == (encode_only ? 1 : 0) && !h->plans.empty();
+        const bool hit = h->plan_ws == workspace && h->plan_B == B && h->plan_T == T && h->plan_mode == mode && !h->plans.empty();
         if (!hit) {
             for (auto* p : h->plans) tc_gemm_plan_destroy(p);
             h->plans.clear();
@@ -408,7 +448,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
             for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
             h->llplans.clear();
             r.building_plans = true;
-            h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_mode = encode_only ? 1 : 0;
+            h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_mode = mode;
         }
     }
 
@@ -420,9 +460,9 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     // ---- encoder (reference encoder.py:53-97) ----
     r.mark(AVC_PHASE_LAYOUT);
     r.check(launch_pack_input(x, c_org, w.X0, at, B, T, E, r.s), "pack_input"); h->launches++;
-    r.gemm(L_ENC_CONV0, w.X0, at, N_MELS + E, M, T, ACT_RELU, w.actA, at, CONV_CH);
-    r.gemm(L_ENC_CONV1, w.actA, at, CONV_CH, M, T, ACT_RELU, w.actB, at, CONV_CH);
-    r.gemm(L_ENC_CONV2, w.actB, at, CONV_CH, M, T, ACT_RELU, w.actA, at, CONV_CH);
+    r.conv_bn(0, w.X0, at, N_MELS + E, M, T, ACT_RELU, w.actA, at, CONV_CH);
+    r.conv_bn(1, w.actA, at, CONV_CH, M, T, ACT_RELU, w.actB, at, CONV_CH);
+    r.conv_bn(2, w.actB, at, CONV_CH, M, T, ACT_RELU, w.actA, at, CONV_CH);
     r.gemm(L_ENC_L0_IH, w.actA, at, CONV_CH, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
     if (r.use_tc() && !h->simt_lstm && enc_lstm_supported(dn)) {
         // register-resident BiLSTM kernels; layer 1 samples the codes and writes the decoder input itself
@@ -447,9 +487,9 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         // ---- decoder (reference decoder.py:58-79) ----
         r.gemm(L_DEC_LSTM1_IH, w.Dm, at, 2 * dn + E, B * nb, nb, ACT_NONE, w.Gd1, DT_F32, 4 * P);
         r.lstm(L_DEC_LSTM1_HH, w.Gd1, DT_F32, nb, d.freq, w.H1, at, P, 1);
-        r.gemm(L_DEC_CONV0, w.H1, at, P, M, T, ACT_RELU, w.actA, at, P);
-        r.gemm(L_DEC_CONV1, w.actA, at, P, M, T, ACT_RELU, w.actB, at, P);
-        r.gemm(L_DEC_CONV2, w.actB, at, P, M, T, ACT_RELU, w.actA, at, P);
+        r.conv_bn(3, w.H1, at, P, M, T, ACT_RELU, w.actA, at, P);
+        r.conv_bn(4, w.actA, at, P, M, T, ACT_RELU, w.actB, at, P);
+        r.conv_bn(5, w.actB, at, P, M, T, ACT_RELU, w.actA, at, P);
         const int g2t = r.gx_type(L_DEC_L2_0_HH, at, LSTM2_H);
         r.gemm(L_DEC_L2_0_IH, w.actA, at, P, M, T, ACT_NONE, w.G2, g2t, 4 * LSTM2_H);
         r.lstm(L_DEC_L2_0_HH, w.G2, g2t, T, 1, w.H2a, at, LSTM2_H, 1);
@@ -458,11 +498,11 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         // linear projection -> mel (B,80,T) fp32 + channel-last copy for the postnet (decoder.py:77, model.py:127)
         r.gemm(L_DEC_LINEAR, w.H2b, at, LSTM2_H, M, T, ACT_NONE, w.melc, pt, N_MELS, mel, nullptr);
         // ---- postnet + residual (reference postnet.py:50-63, model.py:131-132) ----
-        r.gemm(L_POST_CONV0, w.melc, pt, N_MELS, M, T, ACT_TANH, w.actA, pt, CONV_CH);
-        r.gemm(L_POST_CONV1, w.actA, pt, CONV_CH, M, T, ACT_TANH, w.actB, pt, CONV_CH);
-        r.gemm(L_POST_CONV2, w.actB, pt, CONV_CH, M, T, ACT_TANH, w.actA, pt, CONV_CH);
-        r.gemm(L_POST_CONV3, w.actA, pt, CONV_CH, M, T, ACT_TANH, w.actB, pt, CONV_CH);
-        r.gemm(L_POST_CONV4, w.actB, pt, CONV_CH, M, T, ACT_NONE, nullptr, DT_F32, 0, mel_post, mel);
+        r.conv_bn(6, w.melc, pt, N_MELS, M, T, ACT_TANH, w.actA, pt, CONV_CH);
+        r.conv_bn(7, w.actA, pt, CONV_CH, M, T, ACT_TANH, w.actB, pt, CONV_CH);
+        r.conv_bn(8, w.actB, pt, CONV_CH, M, T, ACT_TANH, w.actA, pt, CONV_CH);
+        r.conv_bn(9, w.actA, pt, CONV_CH, M, T, ACT_TANH, w.actB, pt, CONV_CH);
+        r.conv_bn(10, w.actB, pt, CONV_CH, M, T, ACT_NONE, nullptr, DT_F32, 0, mel_post, mel);
     }
     r.mark(AVC_PHASE_COUNT);  // closing marker
     if (!r.ok() && r.building_plans) {  // do not keep a half-built plan set
@@ -564,7 +604,7 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
 // ---------------------------------------------------------------------------------------------
 extern "C" {
 
-int avc_abi_version(void) { return 4; }
+int avc_abi_version(void) { return 5; }
 
 int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision) {
     if (!out || !dims) return fail(nullptr, AVC_ERR_INVALID_ARG, "null out/dims");
@@ -634,18 +674,43 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
     ok = ok && pack_conv(h, L[L_POST_CONV2], "postnet.convolutions.2", CONV_CH, CONV_CH);
     ok = ok && pack_conv(h, L[L_POST_CONV3], "postnet.convolutions.3", CONV_CH, CONV_CH);
     ok = ok && pack_conv(h, L[L_POST_CONV4], "postnet.convolutions.4", CONV_CH, N_MELS);
+    // the same convolutions without the fold + the BatchNorm affine parameters, for the batch-statistics forward
+    static const char* kBnPrefix[N_BN] = {"encoder.convolutions.0", "encoder.convolutions.1", "encoder.convolutions.2",
+                                          "decoder.convolutions.0", "decoder.convolutions.1", "decoder.convolutions.2",
+                                          "postnet.convolutions.0", "postnet.convolutions.1", "postnet.convolutions.2",
+                                          "postnet.convolutions.3", "postnet.convolutions.4"};
+    std::vector<float> bn_gamma[N_BN], bn_beta[N_BN];
+    for (int i = 0; ok && i < N_BN; ++i) {
+        const Layer& F = L[kBnFolded[i]];
+        ok = pack_conv(h, L[L_RAW_CONV0 + i], kBnPrefix[i], F.Cin, F.N, false);
+        if (F.N > BN_MAX_CH) { ok = false; fail(h, AVC_ERR_UNSUPPORTED, "conv width %d exceeds %d", F.N, BN_MAX_CH); }
+        if (ok) { bn_gamma[i] = h->raw[std::string(kBnPrefix[i]) + ".1.weight"]; bn_beta[i] = h->raw[std::string(kBnPrefix[i]) + ".1.bias"]; }
+    }
     if (!ok) { h->loaded = false; return AVC_ERR_MISSING_WEIGHT; }
     h->raw.clear();
     for (int i = 0; i < L_GEN_COUNT; ++i) {
         const bool post = i >= L_POST_CONV0;
         L[i].w_type = h->precision == AVC_PREC_FP32 ? DT_F32 : (post ? DT_F16 : DT_BF16);
     }
+    for (int i = 0; i < N_BN; ++i) L[L_RAW_CONV0 + i].w_type = L[kBnFolded[i]].w_type;
     if (h->device >= 0) {
         cudaError_t e = cudaSetDevice(h->device);
         if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
         for (int i = 0; i < L_GEN_COUNT; ++i) {
             int rc = upload_layer(h, L[i]);
             if (rc != AVC_OK) return rc;
+        }
+        for (int i = 0; i < N_BN; ++i) {
+            int rc = upload_layer(h, L[L_RAW_CONV0 + i]);
+            if (rc != AVC_OK) return rc;
+            for (int k = 0; k < 2; ++k) {
+                float*& dst = k ? h->bn_beta_dev[i] : h->bn_gamma_dev[i];
+                const std::vector<float>& src = k ? bn_beta[i] : bn_gamma[i];
+                if (dst) { cudaFree(dst); dst = nullptr; }
+                e = cudaMalloc((void**)&dst, src.size() * 4);
+                if (e == cudaSuccess) e = cudaMemcpy(dst, src.data(), src.size() * 4, cudaMemcpyHostToDevice);
+                if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "uploading BatchNorm parameters: %s", cudaGetErrorString(e));
+            }
         }
         for (auto* p : h->plans) tc_gemm_plan_destroy(p);
         h->plans.clear();
@@ -672,6 +737,12 @@ int avc_forward(avc_handle h, const float* x, const float* c_org, const float* c
 int avc_encode(avc_handle h, const float* x, const float* c_org, int B, int T, float* codes, void* workspace,
                size_t workspace_bytes, void* stream) {
     return run(h, x, c_org, nullptr, B, T, nullptr, nullptr, codes, workspace, workspace_bytes, stream, true);
+}
+
+int avc_forward_bn_train(avc_handle h, const float* x, const float* c_org, const float* c_trg, int B, int T, float* mel,
+                         float* mel_post, float* codes, float* bn_stats, void* workspace, size_t workspace_bytes, void* stream) {
+    const bool encode_only = c_trg == nullptr;
+    return run(h, x, c_org, c_trg, B, T, mel, mel_post, codes, workspace, workspace_bytes, stream, encode_only, true, bn_stats);
 }
 
 int64_t avc_last_launch_count(avc_handle h) { return h ? h->launches : 0; }
@@ -803,6 +874,10 @@ void avc_destroy(avc_handle h) {
         for (int i = 0; i < L_COUNT; ++i) {
             if (h->layers[i].w_dev) cudaFree(h->layers[i].w_dev);
             if (h->layers[i].b_dev) cudaFree(h->layers[i].b_dev);
+        }
+        for (int i = 0; i < N_BN; ++i) {
+            if (h->bn_gamma_dev[i]) cudaFree(h->bn_gamma_dev[i]);
+            if (h->bn_beta_dev[i]) cudaFree(h->bn_beta_dev[i]);
         }
         for (auto* p : h->plans) tc_gemm_plan_destroy(p);
         for (auto* p : h->lplans) tc_lstm_plan_destroy(p);

@@ -17,6 +17,26 @@ cudaError_t launch_cast_pad_rows(const float* in, void* out, int out_type, long 
 cudaError_t launch_l2norm_rows(const float* in, float* out, int rows, int D, cudaStream_t s);
 cudaError_t launch_segment_mean_renorm(const float* emb, const int* offsets, float* out, int S, int D, cudaStream_t s);
 
+// batchnorm.cu (train-mode BatchNorm1d forward on fp32 conv rows)
+constexpr int BN_MAX_CHUNKS = 1024;
+struct BnTrainParams {
+    const float* Z;          // [M][N] fp32 rows: conv output + bias
+    int M, N, T;             // T: frames per utterance (channel-first output only)
+    const float* gamma;      // [N] BatchNorm weight
+    const float* beta;       // [N] BatchNorm bias
+    float eps;
+    double* partial;         // scratch [bn_chunks(M)][2][N]
+    float* scale_shift;      // scratch [2][N]
+    float* stat_mean;        // optional out [N]: batch mean
+    float* stat_var;         // optional out [N]: biased batch variance
+    int act;
+    void* out; int out_type; // row-major [M][N] output, or
+    float* out_t;            // channel-first fp32 [M/T][N][T] output (+ res_t)
+    const float* res_t;
+};
+int bn_chunks(int M);
+cudaError_t launch_bn_train(const BnTrainParams& p, cudaStream_t s, int* launches);
+
 // tc_gemm.cu (tcgen05 + TMA implicit-GEMM)
 struct TcGemmPlan;  // opaque: tensor maps + tiling for one (layer, B, T) instance
 // Returns nullptr and sets *err when the shape is not supported by the tensor-core kernel.

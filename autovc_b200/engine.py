@@ -69,9 +69,13 @@ class Engine:
             self._ws = torch.empty(need, dtype=torch.uint8, device=torch.device("cuda", self.device_index))
         return self._ws
 
-    def forward(self, x: torch.Tensor, c_org: torch.Tensor, c_trg: Optional[torch.Tensor], out=None):
+    N_BN, BN_MAX_CH = 11, 512     # BatchNorm layers on the path (encoder 0-2, decoder 0-2, postnet 0-4), widest layer
+
+    def forward(self, x: torch.Tensor, c_org: torch.Tensor, c_trg: Optional[torch.Tensor], out=None, bn_train: bool = False):
         """`out`: optional preallocated (mel, mel_post, codes) float32 CUDA tensors of the result shapes (steady-state
-        pipelines that must not touch the allocator); default: fresh tensors, like the reference."""
+        pipelines that must not touch the allocator); default: fresh tensors, like the reference.
+        `bn_train`: BatchNorm with batch statistics (avc_forward_bn_train); the result gains a trailing (11,2,512) tensor
+        of per-layer batch mean / biased variance (rows of layers that did not run are NaN)."""
         B, n_mels, T = x.shape
         dn, E, _, freq = self.dims
         if n_mels != 80 or c_org.shape != (B, E) or (c_trg is not None and c_trg.shape != (B, E)):
@@ -84,6 +88,21 @@ class Engine:
         codes = torch.empty(B, n_codes, dtype=torch.float32, device=dev)
         ws = self._workspace(B, T)
         stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        if bn_train:
+            stats = torch.full((self.N_BN, 2, self.BN_MAX_CH), float("nan"), dtype=torch.float32, device=dev)
+            if c_trg is None:
+                mel = post = None
+            elif out is not None:
+                mel, post, codes = out
+            else:
+                mel = torch.empty(B, 80, T, dtype=torch.float32, device=dev)
+                post = torch.empty(B, 80, T, dtype=torch.float32, device=dev)
+            rc = L.lib().avc_forward_bn_train(self._h, x.data_ptr(), c_org.data_ptr(), c_trg.data_ptr() if c_trg is not None else None,
+                                              B, T, mel.data_ptr() if mel is not None else None,
+                                              post.data_ptr() if post is not None else None, codes.data_ptr(), stats.data_ptr(),
+                                              ws.data_ptr(), ws.numel(), stream)
+            L.raise_for(rc, self._h)
+            return (codes, stats) if c_trg is None else (mel, post, codes, stats)
         if c_trg is None:
             rc = L.lib().avc_encode(self._h, x.data_ptr(), c_org.data_ptr(), B, T, codes.data_ptr(), ws.data_ptr(),
                                     ws.numel(), stream)
@@ -187,6 +206,8 @@ _lib_def = torch.library.Library("autovc_b200", "DEF")
 _lib_def.define("generator_forward(Tensor x, Tensor c_org, Tensor c_trg, int engine) -> (Tensor, Tensor, Tensor)")
 _lib_def.define("generator_encode(Tensor x, Tensor c_org, int engine) -> Tensor")
 _lib_def.define("speaker_embed(Tensor partials, int engine) -> Tensor")
+_lib_def.define("generator_forward_bn_train(Tensor x, Tensor c_org, Tensor c_trg, int engine) -> (Tensor, Tensor, Tensor, Tensor)")
+_lib_def.define("generator_encode_bn_train(Tensor x, Tensor c_org, int engine) -> (Tensor, Tensor)")
 _lib_def.define("generator_forward_out(Tensor x, Tensor c_org, Tensor c_trg, Tensor(a!) mel, Tensor(b!) post, Tensor(c!) codes, int engine) -> ()")
 
 
@@ -200,6 +221,14 @@ def _forward_cuda(x, c_org, c_trg, engine: int):
 
 def _encode_cuda(x, c_org, engine: int):
     return _ENGINES[engine].forward(_prep(x), _prep(c_org), None)
+
+
+def _forward_bn_train_cuda(x, c_org, c_trg, engine: int):
+    return _ENGINES[engine].forward(_prep(x), _prep(c_org), _prep(c_trg), bn_train=True)
+
+
+def _encode_bn_train_cuda(x, c_org, engine: int):
+    return _ENGINES[engine].forward(_prep(x), _prep(c_org), None, bn_train=True)
 
 
 def _forward_out_cuda(x, c_org, c_trg, mel, post, codes, engine: int):
@@ -219,8 +248,12 @@ _lib_impl_cuda.impl("generator_forward", _forward_cuda)
 _lib_impl_cuda.impl("generator_encode", _encode_cuda)
 _lib_impl_cuda.impl("speaker_embed", _speaker_embed_cuda)
 _lib_impl_cuda.impl("generator_forward_out", _forward_out_cuda)
+_lib_impl_cuda.impl("generator_forward_bn_train", _forward_bn_train_cuda)
+_lib_impl_cuda.impl("generator_encode_bn_train", _encode_bn_train_cuda)
 _lib_impl_cpu = torch.library.Library("autovc_b200", "IMPL", "CPU")
 _lib_impl_cpu.impl("generator_forward", _no_cpu)
 _lib_impl_cpu.impl("generator_encode", _no_cpu)
 _lib_impl_cpu.impl("speaker_embed", _no_cpu)
 _lib_impl_cpu.impl("generator_forward_out", _no_cpu)
+_lib_impl_cpu.impl("generator_forward_bn_train", _no_cpu)
+_lib_impl_cpu.impl("generator_encode_bn_train", _no_cpu)

@@ -5,6 +5,9 @@ upstream AutoVC calls `Generator`): same constructor defaults, same `forward(x, 
 
 Semantics pinned to the reference module in `.eval()` under `no_grad`: BatchNorm uses running
 statistics and is folded into the convolution weights when the weights are handed to the C library.
+With `batch_stat_bn=True` a module in `.train()` mode runs BatchNorm the way the reference's un-eval()'d module does
+(batch statistics, running buffers updated with momentum 0.1): the forward pair of `AutoEncoder.learn`
+(`model.py:306`, `:201`) and the literal behaviour of the reference's `convert`.  Forward only.
 
 The sub-modules below exist only to own parameters under the reference's names
 (`encoder.convolutions.0.0.conv.weight`, `decoder.linear_projection.linear_layer.weight`, ... - fixed by the
@@ -92,13 +95,14 @@ class AutoEncoder(nn.Module):
     """
 
     def __init__(self, dim_neck: int = 32, dim_emb: int = 256, dim_pre: int = 512, freq: int = 32,
-                 verbose: bool = True, device=None, precision: str = "bf16"):
+                 verbose: bool = True, device=None, precision: str = "bf16", batch_stat_bn: bool = False):
         super().__init__()
         if device is None:
             device = torch.device("cuda" if torch.cuda.is_available() else "cpu")
         self.verbose = verbose
         self.device = device if not isinstance(device, str) else torch.device(device)
         self.precision = precision
+        self.batch_stat_bn = batch_stat_bn   # with .train(): BatchNorm uses batch statistics and updates its buffers
         self.logging = {}
         self.dims = (dim_neck, dim_emb, dim_pre, freq)
         self.encoder = Encoder(dim_neck, dim_emb, freq)
@@ -106,26 +110,31 @@ class AutoEncoder(nn.Module):
         self.postnet = Postnet()
         self.train(False)  # parity contract: eval-mode BatchNorm
         self._engines: Dict[Tuple[int, str], Engine] = {}
-        self._engine_keys: Dict[Tuple[int, str], int] = {}
+        self._engine_keys: Dict[Tuple[int, str], Tuple[int, int]] = {}
 
     # -- weights -----------------------------------------------------------------------------------
-    def _weights_key(self) -> int:
-        """Changes whenever a parameter/buffer is modified in place or replaced."""
-        k = 0
-        for t in self.state_dict(keep_vars=True).values():
-            k = (k * 1000003 + t._version + (t.data_ptr() & 0xFFFFFFF)) & 0xFFFFFFFFFFFF
-        return k
+    def _weights_key(self) -> Tuple[int, int]:
+        """(all tensors, all but the BatchNorm running statistics): each changes whenever one of its tensors is modified
+        in place or replaced.  The batch-statistics forward does not read the running statistics, so it only needs the
+        second key to be current (it updates those buffers itself after every call)."""
+        k = p = 0
+        for name, t in self.state_dict(keep_vars=True).items():
+            v = t._version + (t.data_ptr() & 0xFFFFFFF)
+            k = (k * 1000003 + v) & 0xFFFFFFFFFFFF
+            if "running_" not in name and "num_batches_tracked" not in name:
+                p = (p * 1000003 + v) & 0xFFFFFFFFFFFF
+        return k, p
 
-    def _engine(self, device: torch.device) -> Engine:
+    def _engine(self, device: torch.device, params_only: bool = False) -> Engine:
         idx = device.index if device.index is not None else torch.cuda.current_device()
         key = (idx, self.precision)
         eng = self._engines.get(key)
         if eng is None:
             eng = Engine(self.dims, idx, self.precision)
             self._engines[key] = eng
-            self._engine_keys[key] = -1
+            self._engine_keys[key] = (-1, -1)
         wk = self._weights_key()
-        if self._engine_keys[key] != wk:
+        if (self._engine_keys[key][1] != wk[1]) if params_only else (self._engine_keys[key] != wk):
             eng.load_state_dict(self.state_dict())
             self._engine_keys[key] = wk
         return eng
@@ -139,6 +148,8 @@ class AutoEncoder(nn.Module):
         Raises ValueError when T < freq, like the reference's torch.cat on an empty list."""
         if not x.is_cuda:
             raise RuntimeError("autovc_b200.AutoEncoder runs on CUDA (sm_100a) only; move the inputs to the GPU")
+        if self.training and self.batch_stat_bn:
+            return self._forward_bn_train(x, c_org, c_trg)
         eng = self._engine(x.device)
         c_org = c_org.to(x.device)
         if c_trg is None:
@@ -148,6 +159,31 @@ class AutoEncoder(nn.Module):
             return out
         mel, post, codes = torch.ops.autovc_b200.generator_forward(x, c_org, c_trg.to(x.device), eng.id)
         return mel, post, codes
+
+    def _bn_modules(self):
+        return [blk[1] for blk in list(self.encoder.convolutions) + list(self.decoder.convolutions) + list(self.postnet.convolutions)]
+
+    def _forward_bn_train(self, x: torch.Tensor, c_org: torch.Tensor, c_trg: Optional[torch.Tensor]):
+        """BatchNorm in training mode (reference: the module as constructed, `model.py:306,201`).  The kernels return
+        each layer's batch mean / biased variance; the running buffers are updated here exactly like nn.BatchNorm1d
+        (momentum 0.1, unbiased variance, num_batches_tracked += 1) - layers 0-2 only for the encode-only call."""
+        eng = self._engine(x.device, params_only=True)
+        c_org = c_org.to(x.device)
+        if c_trg is None:
+            codes, stats = torch.ops.autovc_b200.generator_encode_bn_train(x, c_org, eng.id)
+            res, n_layers = codes, 3
+        else:
+            mel, post, codes, stats = torch.ops.autovc_b200.generator_forward_bn_train(x, c_org, c_trg.to(x.device), eng.id)
+            res, n_layers = (mel, post, codes), 11
+        n = x.shape[0] * x.shape[2]
+        with torch.no_grad():
+            for i, bn in enumerate(self._bn_modules()[:n_layers]):
+                C, m = bn.num_features, bn.momentum
+                mean, var = stats[i, 0, :C].to(bn.running_mean.device), stats[i, 1, :C].to(bn.running_var.device)
+                bn.running_mean.mul_(1 - m).add_(mean, alpha=m)
+                bn.running_var.mul_(1 - m).add_(var * (n / max(n - 1, 1)), alpha=m)
+                bn.num_batches_tracked += 1
+        return res
 
     def batch_forward(self, batch: torch.Tensor, c_org: torch.Tensor, c_trg: torch.Tensor, overlap: float = 0.5):
         """reference `AutoEncoder.batch_forward` (`model.py:395-437`): chunks of one utterance as a batch,

@@ -92,6 +92,18 @@ int avc_forward(avc_handle h, const float* x, const float* c_org, const float* c
 int avc_encode(avc_handle h, const float* x, const float* c_org, int B, int T, float* codes,
                void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same forward with BatchNorm in TRAINING mode (batch statistics over (B,T), biased variance, eps 1e-5), i.e. what
+ * the reference module computes while it is in .train() - its state after construction, in AutoEncoder.learn
+ * (model.py:300-321: forward at :306, the content-code re-encode at :201) and in VoiceConverter.convert, which never
+ * calls .eval().  c_trg == NULL selects the encode-only mode (mel / mel_post may be NULL then).
+ *   bn_stats  optional device output [11][2][512] float32: per BatchNorm layer (encoder 0-2, decoder 0-2, postnet 0-4)
+ *             the batch mean and the BIASED batch variance of each channel (first N entries of each row of 512); the
+ *             caller applies the running-statistics update (momentum 0.1, unbiased variance) - the library keeps no
+ *             mutable model state.  Layers that did not run (encode-only: decoder / postnet) are left untouched. */
+int avc_forward_bn_train(avc_handle h, const float* x, const float* c_org, const float* c_trg, int B, int T,
+                         float* mel, float* mel_post, float* codes, float* bn_stats, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
 /* Number of kernel launches the last avc_forward/avc_encode enqueued (for bench.py's gpu_launches). */
 int64_t avc_last_launch_count(avc_handle h);
 
@@ -228,7 +240,7 @@ void avc_voc_destroy(avc_voc_handle h);
 const char* avc_last_error(avc_handle h);
 
 /* ABI version; bumped on any signature change. */
-int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder */
+int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder; 5: avc_forward_bn_train */
 
 #ifdef __cplusplus
 }

@@ -9,6 +9,7 @@ tensor arithmetic (matmul, add, sigmoid, tanh) on CPU tensors - no `nn.Conv1d`, 
 
 * conv1d k=5, stride 1, zero padding 2          reference `autovc/auto_encoder/net_layers.py:39-49`
 * BatchNorm1d in eval mode, eps = 1e-5          reference `encoder.py:46`, `decoder.py:48`, `postnet.py:27,38,47`
+  (and in training mode on batch statistics, `batchnorm_train`: the module as `learn` / `convert` run it)
 * LSTM, gate order i,f,g,o, b_ih + b_hh         reference `encoder.py:51,75`, `decoder.py:37,53,65,74`
 * speaker concat, code sampling                 reference `encoder.py:65-66,94-95`
 * code up-sampling, decoder, postnet, residual  reference `model.py:92-146`, `decoder.py:58-79`, `postnet.py:50-63`
@@ -71,6 +72,24 @@ def batchnorm_eval(x: Tensor, gamma: Tensor, beta: Tensor, mean: Tensor, var: Te
     return (x - mean.view(1, -1, 1)) * inv.view(1, -1, 1) + beta.view(1, -1, 1)
 
 
+def batchnorm_train(x: Tensor, gamma: Tensor, beta: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """nn.BatchNorm1d in training mode on (B,C,T): per-channel mean and BIASED variance over (B,T), eps 1e-5.
+    Returns (y, batch mean, biased batch variance).  reference `encoder.py:46,70` with the module in `.train()`
+    (its state in `AutoEncoder.learn`, `model.py:306,201`, and in the un-eval()'d `convert`)."""
+    mean = x.mean(dim=(0, 2))
+    var = ((x - mean.view(1, -1, 1)) ** 2).mean(dim=(0, 2))
+    y = (x - mean.view(1, -1, 1)) / torch.sqrt(var.view(1, -1, 1) + BN_EPS) * gamma.view(1, -1, 1) + beta.view(1, -1, 1)
+    return y, mean, var
+
+
+def running_stats_update(running_mean: Tensor, running_var: Tensor, mean: Tensor, var_biased: Tensor, n: int,
+                         momentum: float = 0.1) -> Tuple[Tensor, Tensor]:
+    """The buffer update nn.BatchNorm1d performs after a training-mode forward over n = B*T values per channel:
+    running = (1-m)*running + m*stat, with the UNBIASED variance n/(n-1)*var."""
+    return ((1 - momentum) * running_mean + momentum * mean,
+            (1 - momentum) * running_var + momentum * var_biased * (n / (n - 1)))
+
+
 def fold_batchnorm(w: Tensor, b: Tensor, gamma: Tensor, beta: Tensor, mean: Tensor, var: Tensor):
     """Fold eval-mode BN into the conv: w' = w*s, b' = (b-mean)*s + beta, s = gamma/sqrt(var+eps)."""
     s = gamma / torch.sqrt(var + BN_EPS)
@@ -121,10 +140,16 @@ def lstm_stack(sd: Dict[str, Tensor], prefix: str, x: Tensor, layers: int, bidir
     return x, h_last
 
 
-def conv_bn_act(sd: Dict[str, Tensor], prefix: str, x: Tensor, act: str, quant: Quant = None) -> Tensor:
+def conv_bn_act(sd: Dict[str, Tensor], prefix: str, x: Tensor, act: str, quant: Quant = None,
+                bn_stats: Optional[dict] = None) -> Tensor:
+    """`bn_stats` (a dict) switches BatchNorm to training mode and receives `prefix -> (mean, biased var)`."""
     y = conv1d_k5(x, sd[f"{prefix}.0.conv.weight"], sd[f"{prefix}.0.conv.bias"], quant, prefix)
-    y = batchnorm_eval(y, sd[f"{prefix}.1.weight"], sd[f"{prefix}.1.bias"],
-                       sd[f"{prefix}.1.running_mean"], sd[f"{prefix}.1.running_var"])
+    if bn_stats is not None:
+        y, m, v = batchnorm_train(y, sd[f"{prefix}.1.weight"], sd[f"{prefix}.1.bias"])
+        bn_stats[prefix] = (m, v)
+    else:
+        y = batchnorm_eval(y, sd[f"{prefix}.1.weight"], sd[f"{prefix}.1.bias"],
+                           sd[f"{prefix}.1.running_mean"], sd[f"{prefix}.1.running_var"])
     if act == "relu":
         return torch.clamp_min(y, 0.0)
     if act == "tanh":
@@ -136,12 +161,12 @@ def conv_bn_act(sd: Dict[str, Tensor], prefix: str, x: Tensor, act: str, quant: 
 # the path
 # --------------------------------------------------------------------------------------------
 def encoder_forward(sd: Dict[str, Tensor], x: Tensor, c_org: Tensor, freq: int = 32,
-                    quant: Quant = None, taps: Optional[dict] = None) -> Tuple[List[Tensor], List[Tensor]]:
+                    quant: Quant = None, taps: Optional[dict] = None, bn_stats: Optional[dict] = None) -> Tuple[List[Tensor], List[Tensor]]:
     """reference `encoder.py:53-97`: returns (codes_forward list, codes_backward list)."""
     B, _, T = x.shape
     h = torch.cat([x, c_org.unsqueeze(-1).expand(-1, -1, T)], dim=1)          # encoder.py:65-66
     for i in range(3):                                                          # encoder.py:69-70
-        h = conv_bn_act(sd, f"encoder.convolutions.{i}", h, "relu", quant)
+        h = conv_bn_act(sd, f"encoder.convolutions.{i}", h, "relu", quant, bn_stats)
         if taps is not None:
             taps[f"encoder.conv{i}"] = h
     out, _ = lstm_stack(sd, "encoder.lstm", h.transpose(1, 2), 2, True, quant, taps)  # encoder.py:71-75
@@ -173,12 +198,12 @@ def upsample_codes(codes_f: List[Tensor], codes_b: List[Tensor], T: int, freq: i
 
 
 def decoder_forward(sd: Dict[str, Tensor], enc_out: Tensor, quant: Quant = None,
-                    taps: Optional[dict] = None) -> Tensor:
+                    taps: Optional[dict] = None, bn_stats: Optional[dict] = None) -> Tensor:
     """reference `decoder.py:58-79`: (B,T,320) -> (B,T,80)."""
     h, _ = lstm_stack(sd, "decoder.lstm1", enc_out, 1, False, quant, taps)     # decoder.py:65
     h = h.transpose(1, 2)
     for i in range(3):                                                          # decoder.py:69-70
-        h = conv_bn_act(sd, f"decoder.convolutions.{i}", h, "relu", quant)
+        h = conv_bn_act(sd, f"decoder.convolutions.{i}", h, "relu", quant, bn_stats)
         if taps is not None:
             taps[f"decoder.conv{i}"] = h
     h, _ = lstm_stack(sd, "decoder.lstm2", h.transpose(1, 2), 2, False, quant, taps)   # decoder.py:74
@@ -187,35 +212,37 @@ def decoder_forward(sd: Dict[str, Tensor], enc_out: Tensor, quant: Quant = None,
     return torch.matmul(_q(h, quant, "decoder.linear:x"), _q(w, quant, "decoder.linear:w").t()) + b   # decoder.py:77
 
 
-def postnet_forward(sd: Dict[str, Tensor], mel: Tensor, quant: Quant = None, taps: Optional[dict] = None) -> Tensor:
+def postnet_forward(sd: Dict[str, Tensor], mel: Tensor, quant: Quant = None, taps: Optional[dict] = None,
+                    bn_stats: Optional[dict] = None) -> Tensor:
     """reference `postnet.py:50-63`."""
     h = mel
     for i in range(4):
-        h = conv_bn_act(sd, f"postnet.convolutions.{i}", h, "tanh", quant)
+        h = conv_bn_act(sd, f"postnet.convolutions.{i}", h, "tanh", quant, bn_stats)
         if taps is not None:
             taps[f"postnet.conv{i}"] = h
-    return conv_bn_act(sd, "postnet.convolutions.4", h, "none", quant)
+    return conv_bn_act(sd, "postnet.convolutions.4", h, "none", quant, bn_stats)
 
 
 def generator_forward(sd: Dict[str, Tensor], x: Tensor, c_org: Tensor, c_trg: Optional[Tensor],
                       freq: int = 32, dtype: torch.dtype = torch.float32, quant: Quant = None,
-                      taps: Optional[dict] = None):
-    """reference `AutoEncoder.forward` (`model.py:68-146`) in eval mode.
+                      taps: Optional[dict] = None, bn_stats: Optional[dict] = None):
+    """reference `AutoEncoder.forward` (`model.py:68-146`) in eval mode; with `bn_stats` (a dict to fill) BatchNorm runs
+    in training mode on batch statistics and the per-layer (mean, biased var) are recorded (see `batchnorm_train`).
 
     Returns (mel_outputs (B,80,T), mel_outputs_postnet (B,80,T), content_codes (B,dn*(nf+nb)))
     or only content_codes when `c_trg is None`."""
     sd = {k: (v.to(dtype) if v.is_floating_point() else v) for k, v in sd.items()}
     x, c_org = x.to(dtype), c_org.to(dtype)
     T = x.shape[-1]
-    codes_f, codes_b = encoder_forward(sd, x, c_org, freq, quant, taps)
+    codes_f, codes_b = encoder_forward(sd, x, c_org, freq, quant, taps, bn_stats)
     codes = content_codes(codes_f, codes_b)
     if c_trg is None:
         return codes
     c_trg = c_trg.to(dtype)
     code_exp = upsample_codes(codes_f, codes_b, T, freq)
     enc_out = torch.cat([code_exp, c_trg.unsqueeze(-1).expand(-1, -1, T)], dim=1)   # model.py:124
-    mel = decoder_forward(sd, enc_out.transpose(1, 2), quant, taps).transpose(2, 1)   # model.py:127
-    mel_post = mel + postnet_forward(sd, mel, quant, taps)                            # model.py:131-132
+    mel = decoder_forward(sd, enc_out.transpose(1, 2), quant, taps, bn_stats).transpose(2, 1)   # model.py:127
+    mel_post = mel + postnet_forward(sd, mel, quant, taps, bn_stats)                            # model.py:131-132
     return mel, mel_post, codes
 
 

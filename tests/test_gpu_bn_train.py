@@ -1,0 +1,102 @@
+"""Train-mode BatchNorm forward on the GPU (C ABI avc_forward_bn_train) against the vectors of the
+unmodified reference in `.train()` mode, the CPU oracle, and the running-buffer contract of nn.BatchNorm1d.
+
+Tolerances.  fp32 validation mode: max-abs <= 1e-4 on mel_outputs and codes (measured 1e-6); <= 2e-4 on
+mel_outputs_postnet, whose values reach |6.5| here and whose golden itself carries 3e-5 of the reference's own fp32
+rounding (the float64 oracle differs from it by that much; measured on the GPU 1.1e-4).  bf16 mode: max-abs(mel_outputs)
+<= 1e-2 and cosine(codes) >= 0.999 as in eval mode; the POSTNET output is held to cosine >= 0.995 per utterance and rms
+error <= 0.1 instead of a max-abs bound: with random-init weights mel_outputs has std 0.056, the postnet's first
+batch-statistics BatchNorm rescales it to unit variance, so the decoder's 4e-3 bf16 error enters the postnet as a 7 %
+relative perturbation.  tests/test_bn_train_oracle.py::test_bf16_train_mode_error_prediction reproduces that on the CPU
+(operand rounding emulated in the oracle: max-abs 0.26, rms 0.046; measured on the B200: 0.29)."""
+import numpy as np
+import pytest
+import torch
+
+from autovc_b200.synth import synth_inputs, synth_state_dict
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["bn_train_b4_t64", "bn_train_b3_t100_w3"]
+BN_PREFIXES = [f"encoder.convolutions.{i}" for i in range(3)] + [f"decoder.convolutions.{i}" for i in range(3)] + \
+              [f"postnet.convolutions.{i}" for i in range(5)]
+
+
+def _model(precision, wseed):
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cuda", verbose=False, precision=precision, batch_stat_bn=True)
+    m.load_state_dict(synth_state_dict(wseed))
+    m.train()
+    return m
+
+
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_forward_pair_matches_reference_golden(name, precision):
+    g = load_golden(name)
+    B, T = int(g["B"]), int(g["T"])
+    m = _model(precision, int(g["wseed"]))
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(B, T, seed=int(g["xseed"])))
+    mel, post, codes = m(x, c_org, c_trg)
+    torch.cuda.synchronize()
+    err = {k: float((v.cpu() - torch.from_numpy(g[n])).abs().max()) for k, v, n in (("mel", mel, "mel"), ("post", post, "mel_post"), ("codes", codes, "codes"))}
+    cos = float(torch.nn.functional.cosine_similarity(codes.cpu(), torch.from_numpy(g["codes"]), dim=1).min())
+    print(f"{name}[{precision}]: {err} cos {cos:.6f}")
+    if precision == "fp32":
+        assert err["mel"] <= 1e-4 and err["codes"] <= 1e-4 and err["post"] <= 2e-4
+    else:
+        ref_post = torch.from_numpy(g["mel_post"])
+        cos_post = float(torch.nn.functional.cosine_similarity(post.cpu().flatten(1), ref_post.flatten(1), dim=1).min())
+        rms = float((post.cpu() - ref_post).pow(2).mean().sqrt())
+        print(f"   post cos {cos_post:.5f} rms {rms:.3e}")
+        assert err["mel"] <= 1e-2 and cos >= 0.999 and cos_post >= 0.995 and rms <= 0.1
+    sd = m.state_dict()
+    rt, at = (1e-4, 1e-5) if precision == "fp32" else (3e-2, 5e-3)
+    for i, p in enumerate(BN_PREFIXES):
+        np.testing.assert_allclose(sd[p + ".1.running_mean"].numpy(), g[f"p1.rm{i}"], atol=at, rtol=rt)
+        np.testing.assert_allclose(sd[p + ".1.running_var"].numpy(), g[f"p1.rv{i}"], atol=at, rtol=rt)
+        assert int(sd[p + ".1.num_batches_tracked"]) == int(g[f"p1.nbt{i}"])
+    # pass 2 of `learn` (model.py:201): re-encode the postnet output, still on batch statistics
+    ref_post = torch.from_numpy(g["mel_post"]).cuda() if precision == "bf16" else post
+    codes2 = m(ref_post, c_org, None)
+    torch.cuda.synchronize()
+    if precision == "fp32":
+        assert float((codes2.cpu() - torch.from_numpy(g["codes_pass2"])).abs().max()) <= 1e-4
+    else:
+        assert float(torch.nn.functional.cosine_similarity(codes2.cpu(), torch.from_numpy(g["codes_pass2"]), dim=1).min()) >= 0.999
+    sd = m.state_dict()
+    for i, p in enumerate(BN_PREFIXES):
+        np.testing.assert_allclose(sd[p + ".1.running_mean"].numpy(), g[f"p2.rm{i}"], atol=at, rtol=rt)
+        assert int(sd[p + ".1.num_batches_tracked"]) == int(g[f"p2.nbt{i}"])
+
+
+def test_eval_after_train_uses_the_updated_running_statistics():
+    """After a batch-statistics forward the buffers changed: the next eval-mode forward must re-fold them."""
+    from oracle import autovc_oracle as O
+    m = _model("fp32", 0)
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(3, 64, seed=9))
+    m(x, c_org, c_trg)
+    m.eval()
+    _, post, _ = m(x, c_org, c_trg)
+    sd = {k: v.cpu() for k, v in m.state_dict().items()}
+    _, ref, _ = O.generator_forward(sd, x.cpu(), c_org.cpu(), c_trg.cpu())
+    assert float((post.cpu() - ref).abs().max()) <= 1e-4
+    _, ref0, _ = O.generator_forward(synth_state_dict(0), x.cpu(), c_org.cpu(), c_trg.cpu())
+    assert float((ref - ref0).abs().max()) > 1e-3      # the update mattered
+
+
+def test_training_shape_batch_statistics_against_oracle_properties():
+    """Config-5 shaped per-GPU batch (B=256, T=128) in bf16: every normalised layer output has the batch statistics the
+    definition demands - checked on the last layer, where they are observable: BN(conv) = mel_post - mel has per-channel
+    mean beta and variance gamma^2 (up to eps) over (B,T)."""
+    m = _model("bf16", 0)
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(256, 128, seed=10))
+    mel, post, codes = m(x, c_org, c_trg)
+    d = (post - mel).double()
+    sd = m.state_dict()
+    gamma, beta = sd["postnet.convolutions.4.1.weight"].double().cuda(), sd["postnet.convolutions.4.1.bias"].double().cuda()
+    mean, var = d.mean(dim=(0, 2)), d.var(dim=(0, 2), unbiased=False)
+    assert float((mean - beta).abs().max()) <= 1e-4
+    assert float((var / gamma ** 2 - 1).abs().max()) <= 1e-3
+    assert m.last_launch_count > 24 + 3 * 11 - 1
