@@ -176,13 +176,17 @@ class AutoEncoder(nn.Module):
             mel, post, codes, stats = torch.ops.autovc_b200.generator_forward_bn_train(x, c_org, c_trg.to(x.device), eng.id)
             res, n_layers = (mel, post, codes), 11
         n = x.shape[0] * x.shape[2]
+        bns = self._bn_modules()[:n_layers]
         with torch.no_grad():
-            for i, bn in enumerate(self._bn_modules()[:n_layers]):
-                C, m = bn.num_features, bn.momentum
-                mean, var = stats[i, 0, :C].to(bn.running_mean.device), stats[i, 1, :C].to(bn.running_var.device)
-                bn.running_mean.mul_(1 - m).add_(mean, alpha=m)
-                bn.running_var.mul_(1 - m).add_(var * (n / max(n - 1, 1)), alpha=m)
-                bn.num_batches_tracked += 1
+            st = stats.to(bns[0].running_mean.device)      # one transfer (the buffers live wherever the module lives)
+            means = [st[i, 0, :bn.num_features] for i, bn in enumerate(bns)]
+            uvars = [st[i, 1, :bn.num_features] for i, bn in enumerate(bns)]
+            m = bns[0].momentum
+            torch._foreach_mul_([bn.running_mean for bn in bns], 1 - m)
+            torch._foreach_add_([bn.running_mean for bn in bns], means, alpha=m)
+            torch._foreach_mul_([bn.running_var for bn in bns], 1 - m)
+            torch._foreach_add_([bn.running_var for bn in bns], uvars, alpha=m * (n / max(n - 1, 1)))
+            torch._foreach_add_([bn.num_batches_tracked for bn in bns], 1)
         return res
 
     def batch_forward(self, batch: torch.Tensor, c_org: torch.Tensor, c_trg: torch.Tensor, overlap: float = 0.5):

@@ -125,6 +125,27 @@ class SpeakerEncoder(nn.Module):
         eng = self._engine(flat.device)
         return eng.se_reduce(partial_embeds, offsets), partial_embeds
 
+    def embed_utterance(self, wav, using_partials: bool = True, return_partials: bool = False, **kwargs):
+        """reference `embed_utterance` (`model.py:136-190`) with the mel front-end on the device too: wav (1-D numpy
+        array or tensor) -> CPU tensor (256,).  `kwargs` go to `compute_partial_slices` like the reference's."""
+        from . import audio
+        if not using_partials:
+            frames = audio.mel_spec_speaker_encoder(wav, cut=False, device=self._dev())
+            embed = self.forward(frames[None, ...].contiguous())[0].cpu()
+            return (embed, None, None) if return_partials else embed
+        frames_batch, wave_slices, _ = audio.mel_spec_speaker_encoder(wav, cut=True, return_slices=True, device=self._dev(), **kwargs)
+        embeds, partial_embeds = self._embed_groups([torch.stack(frames_batch)])
+        if return_partials:
+            return embeds[0].cpu(), partial_embeds.cpu(), wave_slices
+        return embeds[0].cpu()
+
+    def embed_utterances(self, wavs: Sequence, **kwargs) -> torch.Tensor:
+        """The batching the reference leaves as a TODO (`model.py:141`): the partial utterances of ALL wavs run through
+        the LSTM stack as one batch.  -> CUDA tensor (len(wavs), 256), row i = `embed_utterance(wavs[i])`."""
+        from . import audio
+        groups = [torch.stack(audio.mel_spec_speaker_encoder(w, cut=True, device=self._dev(), **kwargs)) for w in wavs]
+        return self._embed_groups(groups)[0]
+
     def learn_speaker(self, speaker: Hashable, frames_batches: Sequence) -> torch.Tensor:
         """reference `learn_speaker` (`model.py:446-460`) from mel partials instead of a folder of wavs: the mean (not
         renormalised, as in the reference) of the utterance embeddings, cached in `self.speakers`."""

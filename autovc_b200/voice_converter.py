@@ -10,8 +10,10 @@
 * under `torch.distributed` every rank converts a contiguous block of the work list with replicated weights and no
   collective on the data path; an optional final `all_gather_object` returns the complete list on every rank.
 
-Audio I/O, the mel front-end and the vocoder are outside this path: inputs are normalised mels
-`(80, T)`, outputs are `mel_outputs_postnet` `(80, T)` exactly as `convert` hands them to the vocoder (`:170,:175`).
+`VoiceConverter` works on mels: inputs are normalised mels `(80, T)`, outputs are `mel_outputs_postnet` `(80, T)` exactly
+as `convert` hands them to the vocoder (`:170,:175`).  `WavVoiceConverter` is the waveform-level `convert`: mel front-end
+(`audio.py`), d-vector encoder, generator and WaveRNN vocoder chained on the device.  File I/O,
+the `Audio` pre/out-processing pipelines and wandb logging stay outside.
 """
 from __future__ import annotations
 
@@ -177,6 +179,92 @@ class VoiceConverter:
                 for i, r in zip(shard_range(len(pairs), rk, world), block):
                     results[i] = r
         return results
+
+
+class WavVoiceConverter:
+    """Waveform-level conversion: reference `VoiceConverter.convert` (`voice_converter.py:88-211`) from the point where the
+    wavs are loaded (`:140-155`) to the vocoder output (`:170,:175`), every stage on the device:
+
+        target wav -> mel_spec_speaker_encoder(cut) -> SpeakerEncoder partials -> mean + renorm      (`:153`, SE `:136-190`)
+        source wav -> mel_spec_auto_encoder (-> chunks when `cut`)                                    (`:159`)
+        AutoEncoder.forward / batch_forward                                                           (`:163-174`)
+        WaveRNN.generate                                                                              (`:170,:175`)
+
+    `convert_multiple` does that for a work list with the batching of `VoiceConverter` (one embedding per distinct wav,
+    one generator call per length bucket, one vocoder loop over the folds of all results)."""
+
+    def __init__(self, auto_encoder, speaker_encoder, vocoder=None, device: Optional[torch.device] = None, max_batch: int = 256):
+        self.AE, self.SE, self.vocoder = auto_encoder, speaker_encoder, vocoder
+        self.device = torch.device(device) if device is not None else torch.device("cuda")
+        self.mel_level = VoiceConverter(auto_encoder, device=self.device, max_batch=max_batch)
+
+    def _embed(self, speakers: Sequence) -> List[torch.Tensor]:
+        """speaker refs (a key of `SE.speakers`, an embedding tensor, or a wav) -> embeddings; all wavs in one SE batch."""
+        out: List[Optional[torch.Tensor]] = [None] * len(speakers)
+        wav_idx = []
+        for i, sp in enumerate(speakers):
+            if isinstance(sp, torch.Tensor) and sp.dim() == 1 and sp.numel() == self.AE.dims[1]:
+                out[i] = sp.detach().to(torch.float32).cpu()
+            elif isinstance(sp, (str, int)) and sp in getattr(self.SE, "speakers", {}):
+                out[i] = self.SE.speakers[sp]                                      # reference `:150-151`
+            else:
+                wav_idx.append(i)
+        if wav_idx:
+            embeds = self.SE.embed_utterances([speakers[i] for i in wav_idx]).cpu()
+            for j, i in enumerate(wav_idx):
+                out[i] = embeds[j]
+        return out
+
+    def convert_mels(self, source_wavs: Sequence, source_speakers: Sequence, targets: Sequence, cut: bool = False,
+                     overlap: float = 0.5, **mel_kwargs) -> List[torch.Tensor]:
+        """[source wav], [source speaker ref], [target speaker ref] -> [mel_outputs_postnet (80, T_i)] on the device."""
+        from . import audio
+        n = len(source_wavs)
+        embeds = self._embed(list(source_speakers) + list(targets))
+        c_s, c_t = embeds[:n], embeds[n:]
+        if not cut:
+            mels = [audio.mel_spec_auto_encoder(w, device=self.device, **mel_kwargs) for w in source_wavs]
+            return self.mel_level.convert_batch(mels, c_s, c_t)
+        # chunked: every chunk of every utterance is a row of the same batched forward; overlap-average per utterance
+        chunks, owner = [], []
+        for i, w in enumerate(source_wavs):
+            for c in audio.mel_spec_auto_encoder(w, cut=True, device=self.device, overlap=overlap, **mel_kwargs):
+                chunks.append(c); owner.append(i)
+        posts = self.mel_level.convert_batch(chunks, [c_s[i] for i in owner], [c_t[i] for i in owner])
+        return [overlap_average(torch.stack([p for p, o in zip(posts, owner) if o == i]), overlap) for i in range(n)]
+
+    def convert(self, source_wav, target, source_speaker=None, cut: bool = False, overlap: float = 0.5, vocode: bool = True,
+                vocoder_args: Optional[dict] = None, **mel_kwargs):
+        """One conversion.  `source_speaker` defaults to the source wav itself (the intended call the reference has
+        commented out at `:145`).  Returns the waveform (numpy float32) or, with `vocode=False`, the converted mel."""
+        post = self.convert_mels([source_wav], [source_wav if source_speaker is None else source_speaker], [target],
+                                 cut=cut, overlap=overlap, **mel_kwargs)[0]
+        if not vocode:
+            return post
+        if self.vocoder is None:
+            raise RuntimeError("no vocoder was given to WavVoiceConverter")
+        return self.vocoder.generate(post.unsqueeze(0), **(vocoder_args or {}))
+
+    def convert_multiple(self, source_wavs: Sequence, target_wavs: Sequence, match_method: str = "all_combinations",
+                         cut: bool = False, overlap: float = 0.5, vocode: bool = True, vocoder_args: Optional[dict] = None,
+                         **mel_kwargs) -> list:
+        """reference `convert_multiple` (`:346-398`) on waveforms, pairing and order as the reference; each distinct wav
+        is embedded once, and the vocoder runs one loop over the folds of all converted utterances of a length."""
+        pairs = self.mel_level.match(source_wavs, target_wavs, match_method)
+        distinct = list(source_wavs) + list(target_wavs)
+        embeds = self._embed(distinct)
+        ns = len(source_wavs)
+        posts = self.convert_mels([source_wavs[si] for si, _ in pairs], [embeds[si] for si, _ in pairs],
+                                  [embeds[ns + ti] for _, ti in pairs], cut=cut, overlap=overlap, **mel_kwargs)
+        if not vocode:
+            return posts
+        if self.vocoder is None:
+            raise RuntimeError("no vocoder was given to WavVoiceConverter")
+        waves: list = [None] * len(posts)
+        for _, idx in bucket_by_length([p.shape[-1] for p in posts]).items():   # one vocoder loop per length bucket
+            for i, w in zip(idx, self.vocoder.generate_batch([posts[i] for i in idx], **(vocoder_args or {}))):
+                waves[i] = w
+        return waves
 
 
 class HostPipeline:
