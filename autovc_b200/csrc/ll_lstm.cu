@@ -86,6 +86,8 @@ struct LlLstmArgs {
     int approx;                  // 1 (default): gate activations with MUFU.TANH (tanh.approx.f32, abs err ~5e-4: below the bf16 rounding of h;
                                  // measured end-to-end error unchanged); AVC_LSTM_EXACT=1 selects ex2/rcp based sigmoid/tanh
     int canary;                  // AVC_LSTM_CANARY: 0 no canary poll, 1 (default) loader-only warps, 2 all warps (the previous protocol)
+    int gx_late;                 // 1 (default): issue the Gx_t staging after the operand tile is published - fence.proxy.async waits for the
+                                 // warp's outstanding copies, and Gx_t comes from HBM (lstm2: 1.29 -> 1.24 ms); AVC_LSTM_GX_LATE=0: behind the h loads
     long long* trace;            // optional clock64 trace of CTA (0,0) (AVC_LSTM_TRACE=1), nullptr normally
 };
 
@@ -289,7 +291,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 #pragma unroll
                 for (int i = 0; i < NP; ++i)
                     v[i] = ld_strong(src + (size_t)piece_plane(i) * PSTRIDE + piece_row(i) * PLANE_ELEMS);
-                if (epi) stage_gx(t);                  // Gx_t is needed a whole MMA phase from now: issue it behind the h loads
+                if (epi && !a.gx_late) stage_gx(t);    // (A/B knob) Gx_t behind the h loads
                 // the MMAs of step t-1 still read the tiles until acc_full(t-1): normally long past
                 if (t >= 2 && !epi) ptx::mbar_wait(acc_full, (uint32_t)(t - 2) & 1);
                 for (uint32_t spin = 0;; ++spin) {          // pieces not written yet: fetch all of them again, together
@@ -315,6 +317,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 ptx::fence_proxy_async_smem();          // generic-proxy smem writes -> tcgen05.mma (async proxy) reads
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive_cluster(&gfull[warp >> 2], 0u);     // the LEADER's barrier (both CTAs arrive)
+                if (epi && a.gx_late) stage_gx(t);     // needed a whole MMA phase from now; issued after the fence above, which would wait for it
                 if (crank == 0 && warp >= MMA_WARP0) {
                     // Leader CTA, warps 14/15: issue the pair's MMAs of the step, one K half each into its own accumulator,
                     // chunk by chunk in a fixed order (the accumulation order must not depend on timing: results are bitwise
@@ -574,6 +577,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         a.tiles = ceil_div(B, tn); a.tile0 = bs / tn;
         a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
         { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : 1; }
+        { const char* gv = getenv("AVC_LSTM_GX_LATE"); a.gx_late = gv ? atoi(gv) : 1; }
         a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, tn);          // the pair's MMA: M = 256 (128 gate rows per CTA), N = tile width
         plan->args.push_back(a);
         plan->grids.push_back(dim3(G_n, ceil_div(Bc, tn)));

@@ -60,6 +60,19 @@ def test_conv_bn_fold_and_tap_major_packing(host_engine):
     assert host_engine.packed("post.conv4.w").numel() == 80 * 5 * 512
 
 
+def test_unfolded_conv_packing_for_batch_statistics_mode(host_engine):
+    """The train-mode BatchNorm forward (avc_forward_bn_train) runs the convolutions WITHOUT the fold: same tap-major
+    layout, the conv's own weights and bias."""
+    sd = synth_state_dict(0)
+    for blob, p, cin, cp, cout in (("raw.enc.conv0", "encoder.convolutions.0", 336, 384, 512),
+                                   ("raw.dec.conv2", "decoder.convolutions.2", 512, 512, 512),
+                                   ("raw.post.conv4", "postnet.convolutions.4", 512, 512, 80)):
+        packed = host_engine.packed(blob + ".w").view(cout, 5, cp)
+        assert torch.equal(packed[:, :, :cin], sd[p + ".0.conv.weight"].permute(0, 2, 1))
+        assert torch.equal(host_engine.packed(blob + ".b"), sd[p + ".0.conv.bias"])
+    assert not torch.equal(host_engine.packed("raw.enc.conv0.w"), host_engine.packed("enc.conv0.w"))
+
+
 def test_lstm_unit_major_gate_packing(host_engine):
     sd = synth_state_dict(0)
     H = 1024
