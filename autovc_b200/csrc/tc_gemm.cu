@@ -287,11 +287,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         }
                     }
                     if (a.out_t) {
+                        // residual first, all 16 loads in flight (read-only path: `mel` was written by an earlier kernel); interleaved
+                        // with the stores they serialise behind one another - the compiler must assume out_t and res_t alias -
+                        // and the epilogue of the last postnet layer took 33 us per tile
+                        float rv[16];
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const size_t o = ot_base + (size_t)(n + j) * a.T;
-                            a.out_t[o] = v[j] + (a.res_t ? a.res_t[o] : 0.0f);
-                        }
+                        for (int j = 0; j < 16; ++j) rv[j] = a.res_t ? __ldg(a.res_t + ot_base + (size_t)(n + j) * a.T) : 0.0f;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) a.out_t[ot_base + (size_t)(n + j) * a.T] = v[j] + rv[j];
                     }
                 }
             }
