@@ -1,10 +1,10 @@
 // Encoder BiLSTM recurrence (reference encoder.py:51,74-77: nn.LSTM(512, 32, 2, bidirectional)), H = 32.
 //
 // The recurrent matrix is tiny (128 x 32 per direction), the chains (utterance x direction) are independent, so
-// there is nothing to exchange between CTAs: one WARP owns 8 utterances of one direction for the whole sequence.
-// W_hh lives in registers as mma.sync B fragments (64 registers), the cell state and h stay in registers, and the
-// unit/gate permutation below makes the accumulator fragment of step t exactly the A fragment of step t+1, so a
-// step is 32 HMMA + the gate math with no shuffle, no shared memory and no barrier.
+// there is nothing to exchange between CTAs: a group of four warps owns 8 utterances of one direction for the whole
+// sequence.  W_hh lives in registers as mma.sync B fragments (16 registers per warp), the cell state and h stay in
+// registers, and the unit/gate permutation below makes a thread's accumulator values of step t exactly its A-fragment
+// values of step t+1: a step is 8 HMMA + the gate math of two units per thread and one 32-bit exchange between the warps.
 //
 //   D tile j (8 columns), thread (g = lane/4, q = lane%4) holds columns 2q,2q+1 for row g (rows 8..15 unused)
 //   column c of tile j  <->  unit (c/2)*8 + j/2, gate (j%2)*2 + c%2        => thread q owns units q*8 .. q*8+7,
@@ -49,35 +49,39 @@ struct EncLstmArgs {
     int B, T, freq;
 };
 
-// One warp = 8 utterances (rows g = lane/4 of the m16 tile; rows 8..15 stay zero: the chains are latency-bound, so
-// halving the per-thread gate math is worth more than filling the tile) of one direction.
+// A group of NW = 4 warps = 8 utterances (rows g = lane/4 of the m16 tile; rows 8..15 stay zero: the chains are
+// latency-bound, so halving the per-thread gate math is worth more than filling the tile) of one direction.  Warp v owns
+// units q*8 + 2v, q*8 + 2v + 1 of every thread position: 8 of the 32 HMMAs and 10 of the 40 MUFU ops of a step.  Its packed
+// (h[2v], h[2v+1]) is exactly one of the four A-fragment registers of the next step, so the exchange between the warps is one
+// 32-bit shared-memory word per thread, one barrier, four 32-bit reads (double-buffered by step parity).  The arithmetic per
+// unit is unchanged, so the results are bitwise those of the one-warp-per-chain version (0.52 us/step).
+constexpr int NW = 4;
 template <bool kCodes>
-__global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
-    const int lane = threadIdx.x;
+__global__ void __launch_bounds__(32 * NW) enc_lstm_kernel(const EncLstmArgs a) {
+    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
     const int g = lane >> 2, q = lane & 3;
     const int dir = blockIdx.y;
     const int b = blockIdx.x * 8 + g;
     const bool ok = b < a.B;
 
-    // resident B fragments: tile j, k-step s -> W[row(j, g)][q*8 + 4s .. +3]
-    uint32_t wb[16][2][2];
+    // resident B fragments of this warp's tiles j = 4v .. 4v+3 (units 2v, 2v+1: tiles (i,f) and (g,o) each), k-step s
+    uint32_t wb[4][2][2];
     const __nv_bfloat16* W = a.Whh + (size_t)dir * 4 * EH * EH;
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
+    for (int jj = 0; jj < 4; ++jj) {
+        const int j = 4 * wv + jj;
         const int unit = (g >> 1) * 8 + (j >> 1), gate = (j & 1) * 2 + (g & 1);
         const __nv_bfloat16* wr = W + (size_t)(unit * 4 + gate) * EH + q * 8;
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
             const uint2 v = *reinterpret_cast<const uint2*>(wr + 4 * s);
-            wb[j][s][0] = v.x;
-            wb[j][s][1] = v.y;
+            wb[jj][s][0] = v.x;
+            wb[jj][s][1] = v.y;
         }
     }
 
-    float c[8];
+    float c[2] = {0.f, 0.f};
     uint32_t af[2][4];                       // A fragments of h_{t-1} for the two k-steps (a1, a3 = rows 8..15 = 0)
-#pragma unroll
-    for (int w = 0; w < 8; ++w) c[w] = 0.f;
 #pragma unroll
     for (int s = 0; s < 2; ++s)
 #pragma unroll
@@ -85,78 +89,74 @@ __global__ void __launch_bounds__(32) enc_lstm_kernel(const EncLstmArgs a) {
 
     const int nf = a.T / a.freq, nb = (a.T + a.freq - 1) / a.freq;
     const size_t gx_pitch = (size_t)a.T * 8 * EH;            // floats per utterance
-    const float* gx = a.Gx + (size_t)(ok ? b : 0) * gx_pitch + dir * 4 * EH + q * 32;
+    const float* gx = a.Gx + (size_t)(ok ? b : 0) * gx_pitch + dir * 4 * EH + q * 32 + 8 * wv;   // units 2v, 2v+1: 8 floats
 
     // software pipeline: the hoisted input projections of the next NST-1 steps are in flight (cp.async into a private
-    // shared-memory ring, [stage][w][lane] so that the 16-byte reads are conflict-free) while a step is computed: an L2 hit
-    // costs 1.1-1.3k cycles on this part, about one step of this kernel
+    // shared-memory ring, [stage][piece][thread] so that the 16-byte reads are conflict-free) while a step is computed: an L2
+    // hit costs 1.1-1.3k cycles on this part, several steps of this kernel
     constexpr int NST = 8;
-    __shared__ float4 ring[NST][8][32];
+    __shared__ float4 ring[NST][2][32 * NW];
+    __shared__ uint32_t hx[2][NW][32];
     auto prefetch = [&](int step) {
         if (step < a.T) {
             const int tt = dir == 0 ? step : a.T - 1 - step;
             const float* p = gx + (size_t)tt * 8 * EH;
 #pragma unroll
-            for (int w = 0; w < 8; ++w)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(&ring[step % NST][w][lane])), "l"(p + 4 * w) : "memory");
+            for (int w = 0; w < 2; ++w)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(&ring[step % NST][w][threadIdx.x])), "l"(p + 4 * w) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");      // one group per step, empty past the end
     };
 #pragma unroll
     for (int i = 0; i < NST - 1; ++i) prefetch(i);
 
-    auto do_step = [&](int step, const float4 (&x)[8]) {
+    for (int step = 0; step < a.T; ++step) {
+        prefetch(step + NST - 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(NST - 1) : "memory");   // this thread's pieces of `step` have landed
         const int t = dir == 0 ? step : a.T - 1 - step;
-        float h[8];
+        float h[2];
 #pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            // tiles 2w (i,f) and 2w+1 (g,o) of unit q*8+w
+        for (int w = 0; w < 2; ++w) {
+            const float4 x = ring[step % NST][w][threadIdx.x];
+            // tiles (i,f) and (g,o) of unit q*8 + 2v + w
             float d_if[4] = {0.f, 0.f, 0.f, 0.f}, d_go[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
             for (int s = 0; s < 2; ++s) {
                 mma_bf16_16816(d_if, af[s], wb[2 * w][s][0], wb[2 * w][s][1]);
                 mma_bf16_16816(d_go, af[s], wb[2 * w + 1][s][0], wb[2 * w + 1][s][1]);
             }
-            const float ig = fast_sigmoid(d_if[0] + x[w].x), fg = fast_sigmoid(d_if[1] + x[w].y);
-            const float gg = fast_tanh(d_go[0] + x[w].z), og = fast_sigmoid(d_go[1] + x[w].w);
+            const float ig = fast_sigmoid(d_if[0] + x.x), fg = fast_sigmoid(d_if[1] + x.y);
+            const float gg = fast_tanh(d_go[0] + x.z), og = fast_sigmoid(d_go[1] + x.w);
             c[w] = fg * c[w] + ig * gg;
             h[w] = og * fast_tanh(c[w]);
         }
-        // next step's A fragments: k-step s, a0 = units (4s, 4s+1), a2 = units (4s+2, 4s+3) of row g
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-            af[s][0] = pack_bf16(h[4 * s + 0], h[4 * s + 1]);
-            af[s][2] = pack_bf16(h[4 * s + 2], h[4 * s + 3]);
-        }
+        // exchange: warp v's pair is A-fragment register (k-step v/2, a0 or a2) of everybody's next step
+        hx[step & 1][wv][lane] = pack_bf16(h[0], h[1]);
+        __syncthreads();
+        af[0][0] = hx[step & 1][0][lane];
+        af[0][2] = hx[step & 1][1][lane];
+        af[1][0] = hx[step & 1][2][lane];
+        af[1][2] = hx[step & 1][3][lane];
         const uint4 v = make_uint4(af[0][0], af[0][2], af[1][0], af[1][2]);
         if constexpr (!kCodes) {
-            // layer 0: h_t (bf16) -> Y[b][t][dir*32 + q*8 .. +7]
-            if (ok) *reinterpret_cast<uint4*>(a.Y + ((size_t)b * a.T + t) * (2 * EH) + dir * EH + q * 8) = v;
+            // layer 0: h_t (bf16) -> Y[b][t][dir*32 + q*8 .. +7]; the warps take turns
+            if (ok && wv == (step & (NW - 1))) *reinterpret_cast<uint4*>(a.Y + ((size_t)b * a.T + t) * (2 * EH) + dir * EH + q * 8) = v;
         } else {
-            // layer 1: code sampling (fp32) + de-duplicated decoder input (bf16)
+            // layer 1: code sampling (fp32, every warp its own two units) + de-duplicated decoder input (bf16, warp 0)
             const bool hit = dir == 0 ? (t % a.freq == a.freq - 1) : (t % a.freq == 0);
             if (hit && ok) {
                 const int j = t / a.freq;
                 const size_t cl = (size_t)EH * (nf + nb);
-                const size_t coff = (dir == 0 ? (size_t)j * EH : (size_t)(nf + j) * EH) + q * 8;
-                float4* cp = reinterpret_cast<float4*>(a.codes + (size_t)b * cl + coff);
-                cp[0] = make_float4(h[0], h[1], h[2], h[3]);
-                cp[1] = make_float4(h[4], h[5], h[6], h[7]);
-                __nv_bfloat16* dp = a.D + ((size_t)b * nb + j) * a.ldd + dir * EH + q * 8;
-                *reinterpret_cast<uint4*>(dp) = v;
-                // the tail segment (t >= freq*nf) repeats the LAST forward code (reference model.py:116-117)
-                if (dir == 0 && j == nf - 1 && nb > nf) *reinterpret_cast<uint4*>(dp + a.ldd) = v;
+                const size_t coff = (dir == 0 ? (size_t)j * EH : (size_t)(nf + j) * EH) + q * 8 + 2 * wv;
+                *reinterpret_cast<float2*>(a.codes + (size_t)b * cl + coff) = make_float2(h[0], h[1]);
+                if (wv == 0) {
+                    __nv_bfloat16* dp = a.D + ((size_t)b * nb + j) * a.ldd + dir * EH + q * 8;
+                    *reinterpret_cast<uint4*>(dp) = v;
+                    // the tail segment (t >= freq*nf) repeats the LAST forward code (reference model.py:116-117)
+                    if (dir == 0 && j == nf - 1 && nb > nf) *reinterpret_cast<uint4*>(dp + a.ldd) = v;
+                }
             }
         }
-    };
-
-    for (int step = 0; step < a.T; ++step) {
-        prefetch(step + NST - 1);
-        asm volatile("cp.async.wait_group %0;" ::"n"(NST - 1) : "memory");   // this thread's pieces of `step` have landed
-        float4 x[8];
-#pragma unroll
-        for (int w = 0; w < 8; ++w) x[w] = ring[step % NST][w][lane];
-        do_step(step, x);
     }
 }
 
@@ -176,7 +176,7 @@ bool enc_lstm_supported(int dim_neck) { return dim_neck == EH; }
 cudaError_t launch_enc_lstm_l0(const float* Gx, const void* Whh_bf16, void* Y_bf16, int B, int T, cudaStream_t s) {
     EncLstmArgs a{};
     a.Gx = Gx; a.Whh = (const __nv_bfloat16*)Whh_bf16; a.Y = (__nv_bfloat16*)Y_bf16; a.B = B; a.T = T; a.freq = 1;
-    enc_lstm_kernel<false><<<dim3(ceil_div(B, 8), 2), 32, 0, s>>>(a);
+    enc_lstm_kernel<false><<<dim3(ceil_div(B, 8), 2), 32 * NW, 0, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -191,7 +191,7 @@ cudaError_t launch_enc_lstm_l1(const float* Gx, const void* Whh_bf16, float* cod
         fill_speaker_kernel<<<B, 256, 0, s>>>(c_trg, a.D, nb, ldd, 2 * EH, E);
         if (launches) ++*launches;
     }
-    enc_lstm_kernel<true><<<dim3(ceil_div(B, 8), 2), 32, 0, s>>>(a);
+    enc_lstm_kernel<true><<<dim3(ceil_div(B, 8), 2), 32 * NW, 0, s>>>(a);
     if (launches) ++*launches;
     return cudaGetLastError();
 }
