@@ -337,6 +337,8 @@ const char* tc_init() {
     cudaFuncSetAttribute(tc_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::SMEM_BYTES);
     cudaFuncSetAttribute(tc_gemm_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::SMEM_BYTES);
     cudaFuncSetAttribute(tc_gemm_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<80>::SMEM_BYTES);
+    cudaFuncSetAttribute(tc_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<64>::SMEM_BYTES);
+    cudaFuncSetAttribute(tc_gemm_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<32>::SMEM_BYTES);
     if (cudaGetLastError() != cudaSuccess) return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
     return nullptr;
 }
@@ -376,7 +378,12 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
 
     // ---- N tiling ----
     int bn;
+    // widest tile that still gives every SM a tile; small batches (latency mode) take narrow tiles: a CTA's time is what it must
+    // take in (A tile + W tile per K block at ~42 B/clk per SM), so more, narrower CTAs shorten the layer although A is re-read
     if (p.N % 256 == 0 && (long)tiles_m * (p.N / 256) >= num_sms) bn = 256;
+    else if (p.N % 128 == 0 && ((long)tiles_m * (p.N / 128) >= num_sms / 2 || getenv("AVC_GEMM_NO_NARROW"))) bn = 128;
+    else if (p.N % 64 == 0 && (long)tiles_m * (p.N / 64) >= num_sms / 2) bn = 64;
+    else if (p.N % 32 == 0 && p.N >= 128) bn = 32;
     else if (p.N % 128 == 0) bn = 128;
     else if (p.N == 80) bn = 80;
     else { delete plan; snprintf(msg, sizeof msg, "N=%d is not a multiple of 128 (or 80)", p.N); return bad(msg); }
@@ -454,6 +461,8 @@ cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t,
     switch (plan->block_n) {
         case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
         case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
+        case 64: tc_gemm_kernel<64><<<plan->grid, 192, Cfg<64>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
+        case 32: tc_gemm_kernel<32><<<plan->grid, 192, Cfg<32>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
         default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
     }
     return cudaGetLastError();
