@@ -578,7 +578,8 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
         // small grids (a single utterance tile of lstm1 / the speaker encoder): no fabric to protect, and the canary is an extra
         // round trip per step for the loader-only warps (lstm1 at B <= 32: 0.313 -> 0.287 ms); at B = 256 it is worth 10 %
-        { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : (G_n * ceil_div(Bc, tn) <= 16 ? 0 : 1); }
+        { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : (G_n * ceil_div(Bc, tn) <= 16 ? 0 : 1);
+          const char* c5 = getenv("AVC_LSTM_CANARY_H512"); if (c5 && H <= 512) a.canary = atoi(c5); }
         { const char* gv = getenv("AVC_LSTM_GX_LATE"); a.gx_late = gv ? atoi(gv) : 1; }
         a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, tn);          // the pair's MMA: M = 256 (128 gate rows per CTA), N = tile width
         plan->args.push_back(a);
