@@ -110,6 +110,9 @@ __global__ void __launch_bounds__(32 * NW) enc_lstm_kernel(const EncLstmArgs a) 
 #pragma unroll
     for (int i = 0; i < NST - 1; ++i) prefetch(i);
 
+    // t % freq and t / freq of the running frame, kept incrementally (a runtime division per step sits in the single
+    // instruction stream of the chain)
+    int tm = dir == 0 ? 0 : (a.T - 1) % a.freq, tj = dir == 0 ? 0 : (a.T - 1) / a.freq;
     for (int step = 0; step < a.T; ++step) {
         prefetch(step + NST - 1);
         asm volatile("cp.async.wait_group %0;" ::"n"(NST - 1) : "memory");   // this thread's pieces of `step` have landed
@@ -143,9 +146,9 @@ __global__ void __launch_bounds__(32 * NW) enc_lstm_kernel(const EncLstmArgs a) 
             if (ok && wv == (step & (NW - 1))) *reinterpret_cast<uint4*>(a.Y + ((size_t)b * a.T + t) * (2 * EH) + dir * EH + q * 8) = v;
         } else {
             // layer 1: code sampling (fp32, every warp its own two units) + de-duplicated decoder input (bf16, warp 0)
-            const bool hit = dir == 0 ? (t % a.freq == a.freq - 1) : (t % a.freq == 0);
+            const bool hit = dir == 0 ? (tm == a.freq - 1) : (tm == 0);
             if (hit && ok) {
-                const int j = t / a.freq;
+                const int j = tj;
                 const size_t cl = (size_t)EH * (nf + nb);
                 const size_t coff = (dir == 0 ? (size_t)j * EH : (size_t)(nf + j) * EH) + q * 8 + 2 * wv;
                 *reinterpret_cast<float2*>(a.codes + (size_t)b * cl + coff) = make_float2(h[0], h[1]);
@@ -156,6 +159,8 @@ __global__ void __launch_bounds__(32 * NW) enc_lstm_kernel(const EncLstmArgs a) 
                     if (dir == 0 && j == nf - 1 && nb > nf) *reinterpret_cast<uint4*>(dp + a.ldd) = v;
                 }
             }
+            if (dir == 0) { if (++tm == a.freq) { tm = 0; ++tj; } }
+            else { if (tm == 0) { tm = a.freq - 1; --tj; } else --tm; }
         }
     }
 }

@@ -576,10 +576,10 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
         a.tiles = ceil_div(B, tn); a.tile0 = bs / tn;
         a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
-        // small grids (a single utterance tile of lstm1 / the speaker encoder): no fabric to protect, and the canary is an extra
-        // round trip per step for the loader-only warps (lstm1 at B <= 32: 0.313 -> 0.287 ms); at B = 256 it is worth 10 %
-        { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : (G_n * ceil_div(Bc, tn) <= 16 ? 0 : 1);
-          const char* c5 = getenv("AVC_LSTM_CANARY_H512"); if (c5 && H <= 512) a.canary = atoi(c5); }
+        // canary poll of the loader-only warps: worth 10 % at H = 1024 with a full grid (without it they hammer the fabric with
+        // 64 KiB waves per CTA while the epilogue runs); at H <= 512 (16 KiB waves) and on small grids it only adds a round trip
+        // per step (lstm1 at B = 256: 0.328 -> 0.308 ms; at B <= 32: 0.313 -> 0.287 ms)
+        { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : (H <= 512 || G_n * ceil_div(Bc, tn) <= 16 ? 0 : 1); }
         { const char* gv = getenv("AVC_LSTM_GX_LATE"); a.gx_late = gv ? atoi(gv) : 1; }
         a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, tn);          // the pair's MMA: M = 256 (128 gate rows per CTA), N = tile width
         plan->args.push_back(a);
