@@ -262,7 +262,7 @@ Workspace carve(const avc_ctx* h, char* base, int B, int T) {
     w.ready_bytes = (size_t)tc_lstm_ready_words(B, T) * 4;
     w.ready = (unsigned int*)take(w.ready_bytes);
     w.Yb = take(tc_lstm_tile_bytes(B, T, hmax));
-    w.bn_partial = (double*)take((size_t)bn_chunks((int)M) * 2 * BN_MAX_CH * sizeof(double));
+    w.bn_partial = (double*)take((size_t)bn_partial_capacity((int)M) * 2 * BN_MAX_CH * sizeof(double));
     w.bn_ss = (float*)take((size_t)2 * BN_MAX_CH * sizeof(float));
     w.total = off;
     return w;
@@ -299,8 +299,9 @@ struct Runner {
     }
 
     // out[m,n] = act(A W^T + b); A is an activation buffer of `a_type`
+    int last_stat_chunks = 0;   // set by gemm(): > 0 when the launch also wrote the BatchNorm column sums
     void gemm(int lid, const void* A, int a_type, int lda, int M, int Tutt, int act, void* out, int out_type, int ldo,
-              float* out_t = nullptr, const float* res_t = nullptr) {
+              float* out_t = nullptr, const float* res_t = nullptr, double* stat_partial = nullptr) {
         if (!ok()) return;
         const Layer& L = h->layers[lid];
         mark(L.taps > 1 ? AVC_PHASE_CONV : AVC_PHASE_PROJ);
@@ -312,6 +313,8 @@ struct Runner {
         p.bias = L.b_dev; p.act = act;
         p.out = out; p.out_type = out_type; p.ldo = ldo;
         p.out_t = out_t; p.res_t = res_t;
+        p.stat_partial = stat_partial; p.stat_capacity = stat_partial ? bn_partial_capacity(M) : 0;
+        last_stat_chunks = 0;
         if (use_tc()) {
             if (building_plans) {
                 const char* why = nullptr;
@@ -319,6 +322,7 @@ struct Runner {
                 if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core GEMM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
                 h->plans.push_back(plan);
             }
+            last_stat_chunks = tc_gemm_plan_stat_chunks(h->plans[plan_cursor]);
             check(launch_tc_gemm(h->plans[plan_cursor++], s, out_t, res_t), L.name.c_str());
         } else {
             check(launch_simt_gemm(p, s), L.name.c_str());
@@ -335,8 +339,10 @@ struct Runner {
         if (!bn_train) { gemm(kBnFolded[bn], A, a_type, lda, M, Tutt, act, out, out_type, ldo, out_t, res_t); return; }
         const Layer& L = h->layers[L_RAW_CONV0 + bn];
         float* Z = wsp->G2;
-        gemm(L_RAW_CONV0 + bn, A, a_type, lda, M, Tutt, ACT_NONE, Z, DT_F32, L.N);
+        gemm(L_RAW_CONV0 + bn, A, a_type, lda, M, Tutt, ACT_NONE, Z, DT_F32, L.N, nullptr, nullptr,
+             getenv("AVC_BN_NO_FUSED_STATS") ? nullptr : wsp->bn_partial);
         if (!ok()) return;
+        const int fused_chunks = last_stat_chunks;
         BnTrainParams q{};
         q.Z = Z; q.M = M; q.N = L.N; q.T = Tutt;
         q.gamma = h->bn_gamma_dev[bn]; q.beta = h->bn_beta_dev[bn]; q.eps = 1e-5f;
@@ -345,7 +351,7 @@ struct Runner {
         q.stat_var = bn_stats ? bn_stats + (size_t)bn * 2 * BN_MAX_CH + BN_MAX_CH : nullptr;
         q.act = act; q.out = out; q.out_type = out_type; q.out_t = out_t; q.res_t = res_t;
         int n = 0;
-        check(launch_bn_train(q, s, &n), "train-mode BatchNorm");
+        check(launch_bn_train(q, s, &n, fused_chunks), "train-mode BatchNorm");
         h->launches += n;
     }
 

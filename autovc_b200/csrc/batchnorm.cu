@@ -150,12 +150,21 @@ int bn_chunks(int M) {
     return chunks < BN_MAX_CHUNKS ? chunks : BN_MAX_CHUNKS;
 }
 
-cudaError_t launch_bn_train(const BnTrainParams& p, cudaStream_t s, int* launches) {
+int bn_partial_capacity(int M) {
+    // the GEMM-fused layout has one chunk per (128-row tile, epilogue warp); tiles may be padded (ragged T), at most 2x
+    const int fused = 8 * ceil_div(M, 128) + 8;
+    const int plain = bn_chunks(M);
+    return fused > plain ? fused : plain;
+}
+
+cudaError_t launch_bn_train(const BnTrainParams& p, cudaStream_t s, int* launches, int fused_chunks) {
     if (p.N % 8 || p.N > 1024 || p.M <= 0) return cudaErrorInvalidValue;
-    const int chunks = bn_chunks(p.M);
-    const int rows_per_chunk = ceil_div(p.M, chunks);
-    const int rpp = BN_THREADS / (p.N / 4);
-    bn_partial_kernel<<<chunks, BN_THREADS, (size_t)rpp * 2 * p.N * sizeof(double), s>>>(p.Z, p.partial, p.M, p.N, rows_per_chunk);
+    const int chunks = fused_chunks > 0 ? fused_chunks : bn_chunks(p.M);
+    if (fused_chunks <= 0) {
+        const int rows_per_chunk = ceil_div(p.M, chunks);
+        const int rpp = BN_THREADS / (p.N / 4);
+        bn_partial_kernel<<<chunks, BN_THREADS, (size_t)rpp * 2 * p.N * sizeof(double), s>>>(p.Z, p.partial, p.M, p.N, rows_per_chunk);
+    }
     bn_finalize_kernel<<<ceil_div(p.N, 32), FIN_WARPS * 32, 0, s>>>(p.partial, chunks, p.M, p.N, p.gamma, p.beta, p.eps, p.scale_shift, p.stat_mean, p.stat_var);
     if (p.out_t) {
         dim3 grid(ceil_div(p.T, 32), p.M / p.T);
@@ -167,7 +176,7 @@ cudaError_t launch_bn_train(const BnTrainParams& p, cudaStream_t s, int* launche
         else if (p.out_type == DT_BF16) bn_apply_kernel<__nv_bfloat16><<<grid, BN_THREADS, 0, s>>>(p.Z, p.scale_shift, (__nv_bfloat16*)p.out, n8, p.N, p.act);
         else bn_apply_kernel<__half><<<grid, BN_THREADS, 0, s>>>(p.Z, p.scale_shift, (__half*)p.out, n8, p.N, p.act);
     }
-    if (launches) *launches = 3;
+    if (launches) *launches = fused_chunks > 0 ? 2 : 3;
     return cudaGetLastError();
 }
 

@@ -40,6 +40,8 @@ struct GemmParams {
     int ldo;
     float* out_t;       // optional channel-first fp32 output [M/T][N][T] (the reference's (B,80,T) layout)
     const float* res_t; // optional residual added to out_t (same layout)
+    double* stat_partial;   // optional (tensor-core path, fp32 rows): fused per-column sums for the train-mode BatchNorm, [chunk][2][N]
+    int stat_capacity;      // chunks the buffer holds
 };
 
 // One time step of an LSTM layer (both directions in one launch, blockIdx.z = direction):

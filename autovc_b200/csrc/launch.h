@@ -35,13 +35,17 @@ struct BnTrainParams {
     const float* res_t;
 };
 int bn_chunks(int M);
-cudaError_t launch_bn_train(const BnTrainParams& p, cudaStream_t s, int* launches);
+int bn_partial_capacity(int M);     // chunks to allocate for BnTrainParams::partial (covers the GEMM-fused layout as well)
+// fused_chunks > 0: `partial` already holds that many chunks written by the GEMM epilogue; the statistics pass is skipped
+cudaError_t launch_bn_train(const BnTrainParams& p, cudaStream_t s, int* launches, int fused_chunks = 0);
 
 // tc_gemm.cu (tcgen05 + TMA implicit-GEMM)
 struct TcGemmPlan;  // opaque: tensor maps + tiling for one (layer, B, T) instance
 // Returns nullptr and sets *err when the shape is not supported by the tensor-core kernel.
 TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** err);
 void tc_gemm_plan_destroy(TcGemmPlan* plan);
+// > 0 when the plan's kernel also writes the BatchNorm column sums (GemmParams::stat_partial): that many chunks
+int tc_gemm_plan_stat_chunks(const TcGemmPlan* plan);
 // out_t/res_t are the caller-owned channel-first output / residual of THIS call (never cached in the plan)
 cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t, const float* res_t);
 // one-time driver entry point lookup; returns nullptr on success or an error string

@@ -42,6 +42,7 @@ struct TcGemmArgs {
     uint32_t idesc_half;
     int tma_out;                         // row-major output leaves through shared memory + TMA stores (tmO)
     int ob_t, ob_b;                      // frames x utterances of one epilogue warp's 32 tile rows
+    double* stat_partial;                // STATS kernels: per (M tile, epilogue warp) column sums / sums of squares [chunk][2][N]
 };
 
 constexpr int OUT_STAGE_BYTES = 32 * 128;         // one epilogue warp's 32 rows x 128 bytes, SWIZZLE_128B
@@ -78,7 +79,9 @@ __device__ __forceinline__ void decode_tile(const TcGemmArgs& a, int tile, int& 
     }
 }
 
-template <int BLOCK_N>
+// STATS: the fp32 row-major epilogue also reduces every staged 32-row block over its rows (per-column sum and sum of squares of
+// the VALID rows) for the train-mode BatchNorm (batchnorm.cu): the statistics pass then never re-reads the conv output.
+template <int BLOCK_N, bool STATS = false>
 __global__ void __launch_bounds__(192, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmO,
                const __grid_constant__ CUtensorMap tmWh, const TcGemmArgs a) {
@@ -242,6 +245,21 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         ptx::tma_store_3d(&tmO, stg + buf, n0 + c0, ct, cb);
                         ptx::bulk_commit_group();
                     }
+                    if constexpr (STATS) {
+                        // lane = column of the staged 32 x 32 fp32 block (swizzled 16-byte pieces: conflict-free), rows in order
+                        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+                        const uint32_t col = ptx::smem_u32(stg) + buf + (uint32_t)((lane & 3) * 4);
+                        float ssum = 0.0f, ssq = 0.0f;
+#pragma unroll
+                        for (int rr2 = 0; rr2 < 32; ++rr2) {
+                            float x;
+                            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(col + (uint32_t)(rr2 * 128) + ((((uint32_t)lane >> 2) ^ (uint32_t)(rr2 & 7)) << 4)));
+                            if ((vmask >> rr2) & 1u) { ssum += x; ssq = fmaf(x, x, ssq); }
+                        }
+                        double* pp = a.stat_partial + ((size_t)(mt * 4 + q) * 2) * a.N + (n0 + c0 + lane);
+                        pp[0] = (double)ssum;
+                        pp[a.N] = (double)ssq;
+                    }
                 }
             } else
 #pragma unroll 1
@@ -325,6 +343,7 @@ struct TcGemmPlan {
     TcGemmArgs args;
     int block_n;
     int grid;
+    int stat_chunks;                     // > 0: the STATS kernel writes this many (M tile x epilogue warp) chunks of column sums
 };
 
 const char* tc_init() {
@@ -336,6 +355,8 @@ const char* tc_init() {
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
     cudaFuncSetAttribute(tc_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::SMEM_BYTES);
     cudaFuncSetAttribute(tc_gemm_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::SMEM_BYTES);
+    cudaFuncSetAttribute(tc_gemm_kernel<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::SMEM_BYTES);
+    cudaFuncSetAttribute(tc_gemm_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::SMEM_BYTES);
     cudaFuncSetAttribute(tc_gemm_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<80>::SMEM_BYTES);
     cudaFuncSetAttribute(tc_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<64>::SMEM_BYTES);
     cudaFuncSetAttribute(tc_gemm_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<32>::SMEM_BYTES);
@@ -432,6 +453,8 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
     }
     // ---- row-major output through TMA stores: one box = an epilogue warp's 32 tile rows x 128 bytes ----
     a.tma_out = 0;
+    a.stat_partial = nullptr;
+    plan->stat_chunks = 0;
     plan->tmO = plan->tmW;
     const int cw = p.out_type == DT_F32 ? 32 : 64;
     if (p.out && bn % cw == 0 && !getenv("AVC_GEMM_NO_TMA_STORE") && ((uintptr_t)p.out % 16) == 0) {
@@ -447,11 +470,17 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { delete plan; snprintf(msg, sizeof msg, "cuTensorMapEncodeTiled(out) failed: %d", (int)r); return bad(msg); }
         a.tma_out = 1;
+        // fused BatchNorm statistics: fp32 rows through the staged epilogue, full- or half-width 256/128 tiles
+        if (p.stat_partial && p.out_type == DT_F32 && (bn == 256 || bn == 128) && tiles_m * 4 <= p.stat_capacity) {
+            a.stat_partial = p.stat_partial;
+            plan->stat_chunks = tiles_m * 4;
+        }
     }
     return plan;
 }
 
 void tc_gemm_plan_destroy(TcGemmPlan* plan) { delete plan; }
+int tc_gemm_plan_stat_chunks(const TcGemmPlan* plan) { return plan->stat_chunks; }
 
 cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t, const float* res_t) {
     // the cached plan owns only workspace/weight addresses; caller-owned output pointers are per call
@@ -459,8 +488,14 @@ cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t,
     args.out_t = out_t;
     args.res_t = res_t;
     switch (plan->block_n) {
-        case 256: tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
-        case 128: tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
+        case 256:
+            if (plan->stat_chunks) tc_gemm_kernel<256, true><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args);
+            else tc_gemm_kernel<256><<<plan->grid, 192, Cfg<256>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args);
+            break;
+        case 128:
+            if (plan->stat_chunks) tc_gemm_kernel<128, true><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args);
+            else tc_gemm_kernel<128><<<plan->grid, 192, Cfg<128>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args);
+            break;
         case 64: tc_gemm_kernel<64><<<plan->grid, 192, Cfg<64>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
         case 32: tc_gemm_kernel<32><<<plan->grid, 192, Cfg<32>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;
         default: tc_gemm_kernel<80><<<plan->grid, 192, Cfg<80>::SMEM_BYTES, s>>>(plan->tmA, plan->tmW, plan->tmO, plan->tmWh, args); break;

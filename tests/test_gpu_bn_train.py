@@ -99,4 +99,4 @@ def test_training_shape_batch_statistics_against_oracle_properties():
     mean, var = d.mean(dim=(0, 2)), d.var(dim=(0, 2), unbiased=False)
     assert float((mean - beta).abs().max()) <= 1e-4
     assert float((var / gamma ** 2 - 1).abs().max()) <= 1e-3
-    assert m.last_launch_count > 24 + 3 * 11 - 1
+    assert m.last_launch_count >= 24 + 2 * 11     # per BatchNorm layer at least finalize + apply on top of the GEMM (statistics fused or not)
