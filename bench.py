@@ -48,19 +48,54 @@ def load_peaks():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks/throttle reasons of one GPU while the timed region runs."""
+    """SM clock and throttle reasons of one GPU, sampled every 5 ms through NVML while the timed region runs (the region is
+    tens of milliseconds: an `nvidia-smi -lms` child process does not even start in that time on an 8-GPU box); falls back to
+    the nvidia-smi loop when the NVML binding is missing."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, index: int):
         self.index = index
         self.rows = []
+        self.samples = []          # (sm_mhz, reasons bitmask) from NVML
         self.proc = None
         self.thread = None
+        self.nvml = None
+        self.handle = None
+        self.max_mhz = None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(index).uuid)
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
 
     def start(self):
+        if self.nvml is not None:
+            nv, h = self.nvml, self.handle
+
+            def poll():
+                while not self._stop.is_set():
+                    try:
+                        self.samples.append((float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)),
+                                             int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))))
+                    except Exception:
+                        pass
+                    time.sleep(0.005)
+
+            self.thread = threading.Thread(target=poll, daemon=True)
+            self.thread.start()
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100"],
@@ -77,6 +112,16 @@ class ClockSampler:
         self.thread.start()
 
     def stop(self):
+        if self.nvml is not None:
+            self._stop.set()
+            if self.thread is not None:
+                self.thread.join(timeout=2)
+            sm = [s for s, _ in self.samples]
+            mask = 0
+            for _, m in self.samples:
+                mask |= m
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz,
+                    "reasons": sorted(n for bit, n in self.REASONS if mask & bit), "samples": len(sm), "source": "nvml, 5 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -99,7 +144,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
 def time_oracle(batch: int, frames: int, steps: int, warmup: int):
