@@ -69,10 +69,32 @@ struct Workspace {
     // all pointers are carved from the caller's workspace; sizes in bytes
     char* X0; char* actA; char* actB; float* GxE; char* Y0; float* Y1; float* cstate;
     char* Dm; float* Gd1; char* H1; float* G2; char* H2a; char* H2b; char* melc;
-    unsigned int* ready; size_t ready_bytes;
-    char* Yb;    // recurrent operand-tile copy of the running LSTM layer's output (tc_lstm.cu)
+    char* Yb;    // exchange copy of the running LSTM layer's output (ll_lstm.cu)
     double* bn_partial; float* bn_ss;   // train-mode BatchNorm scratch (batchnorm.cu); the fp32 conv rows reuse G2
     size_t total;
+};
+
+// mode: 0 forward, 1 encode only, 2 speaker encoder, 3 / 4 forward / encode with batch-statistics BatchNorm
+struct PlanSet {
+    void* ws = nullptr; int B = 0, T = 0, mode = 0;
+    uint64_t stamp = 0;
+    std::vector<TcGemmPlan*> plans;
+    std::vector<LlLstmPlan*> llplans;
+    ~PlanSet() {
+        for (auto* p : plans) tc_gemm_plan_destroy(p);
+        for (auto* p : llplans) ll_lstm_plan_destroy(p);
+    }
+};
+constexpr size_t PLAN_CACHE_ENTRIES = 8;
+
+// restores the caller's current device when an entry point returns (the library switches to the context's device)
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t enter(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        return prev == device ? cudaSuccess : cudaSetDevice(device);
+    }
+    ~DeviceGuard() { int cur = -1; if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev); }
 };
 
 }  // namespace
@@ -92,15 +114,13 @@ struct avc_ctx {
     float* bn_gamma_dev[N_BN] = {};   // BatchNorm weight / bias of the 11 conv blocks (train-mode forward)
     float* bn_beta_dev[N_BN] = {};
     int64_t launches = 0;
-    // tensor-core plan cache (valid for one (B,T,workspace) triple)
-    std::vector<TcGemmPlan*> plans;
-    std::vector<TcLstmPlan*> lplans;
-    std::vector<LlLstmPlan*> llplans;
-    bool old_lstm = false;     // AVC_LSTM_IMPL=tc: step-counter + TMA recurrence (tc_lstm.cu) instead of ll_lstm.cu
+    // tensor-core plan cache: a small LRU of plan sets (tensor maps + launch geometry), one per (workspace, B, T, mode).
+    // Alternating shapes - the converter's length buckets, a B=1 call after a B=256 step, the training pair's
+    // encode-only pass - hit their own entry instead of re-encoding every tensor map.
+    std::vector<PlanSet*> plan_cache;
+    uint64_t plan_clock = 0;
+    int64_t plan_builds = 0;
     bool simt_lstm = false;    // AVC_SIMT_LSTM=1: debugging aid, per-step CUDA-core recurrences in the bf16 mode
-    int plan_B = 0, plan_T = 0;
-    void* plan_ws = nullptr;
-    int plan_mode = 0;         // 0 forward, 1 encode only, 2 speaker encoder, 3 / 4 forward / encode with batch-statistics BatchNorm
     // optional per-phase timing (avc_set_profiling): events at phase boundaries of the last run
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;
@@ -259,9 +279,7 @@ Workspace carve(const avc_ctx* h, char* base, int B, int T) {
     w.H2a = take(M * LSTM2_H * as);
     w.H2b = take(M * LSTM2_H * as);
     w.melc = take(M * N_MELS * as);
-    w.ready_bytes = (size_t)tc_lstm_ready_words(B, T) * 4;
-    w.ready = (unsigned int*)take(w.ready_bytes);
-    w.Yb = take(tc_lstm_tile_bytes(B, T, hmax));
+    w.Yb = take(ll_lstm_exchange_bytes(B, T, hmax));
     w.bn_partial = (double*)take((size_t)bn_partial_capacity((int)M) * 2 * BN_MAX_CH * sizeof(double));
     w.bn_ss = (float*)take((size_t)2 * BN_MAX_CH * sizeof(float));
     w.total = off;
@@ -276,7 +294,8 @@ struct Runner {
     cudaStream_t s;
     int B, T;
     int rc = AVC_OK;
-    size_t plan_cursor = 0, lplan_cursor = 0, llplan_cursor = 0;
+    PlanSet* ps = nullptr;      // the plan set of this (workspace, B, T, mode); filled on its first run
+    size_t plan_cursor = 0, llplan_cursor = 0;
     bool building_plans = false;
 
     bool ok() const { return rc == AVC_OK; }
@@ -320,10 +339,10 @@ struct Runner {
                 const char* why = nullptr;
                 TcGemmPlan* plan = tc_gemm_plan_create(p, h->num_sms, &why);
                 if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core GEMM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
-                h->plans.push_back(plan);
+                ps->plans.push_back(plan);
             }
-            last_stat_chunks = tc_gemm_plan_stat_chunks(h->plans[plan_cursor]);
-            check(launch_tc_gemm(h->plans[plan_cursor++], s, out_t, res_t), L.name.c_str());
+            last_stat_chunks = tc_gemm_plan_stat_chunks(ps->plans[plan_cursor]);
+            check(launch_tc_gemm(ps->plans[plan_cursor++], s, out_t, res_t), L.name.c_str());
         } else {
             check(launch_simt_gemm(p, s), L.name.c_str());
         }
@@ -359,7 +378,7 @@ struct Runner {
     //   Gx: [B][Tg][ndir*4H] fp32 (row for frame t is t/gx_div);  Y: [B][T][ndir*H] of h_type.
     // true when lstm() takes the in-band-exchange tensor-core kernel for this layer (which also accepts fp16 Gx)
     bool ll_path(int lid_hh, int h_type, int H, int ndir) const {
-        return use_tc() && !h->simt_lstm && !h->old_lstm && ndir == 1 && h_type == DT_BF16 && h->layers[lid_hh].w_type == DT_BF16 && H % 256 == 0 && H <= 1024;
+        return use_tc() && !h->simt_lstm && ndir == 1 && h_type == DT_BF16 && h->layers[lid_hh].w_type == DT_BF16 && H % 256 == 0 && H <= 1024;
     }
     // fp16 gate pre-activations for the big recurrent layers: halves the Gx write + read (1 GB per forward at config 2)
     int gx_type(int lid_hh, int h_type, int H) const { return ll_path(lid_hh, h_type, H, 1) && !h->gx_f32 ? DT_F16 : DT_F32; }
@@ -376,28 +395,14 @@ struct Runner {
                 const char* why = nullptr;
                 LlLstmPlan* plan = ll_lstm_plan_create(L.w_dev, Gx_, gx_t, Tg, gx_div, Y, wsp->Yb, B, T, H, h->num_sms, &why);
                 if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core LSTM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
-                h->llplans.push_back(plan);
+                ps->llplans.push_back(plan);
             }
             int n = 0;
-            check(launch_ll_lstm(h->llplans[llplan_cursor++], s, &n), L.name.c_str());
+            check(launch_ll_lstm(ps->llplans[llplan_cursor++], s, &n), L.name.c_str());
             h->launches += n;
             return;
         }
         if (gx_t != DT_F32) { rc = fail(h, AVC_ERR_UNSUPPORTED, "fp16 Gx outside the ll_lstm path"); return; }
-        if (use_tc() && !h->simt_lstm && ndir == 1 && h_type == DT_BF16 && L.w_type == DT_BF16 && H % 64 == 0) {
-            // persistent tensor-core recurrence (tc_lstm.cu)
-            if (building_plans) {
-                const char* why = nullptr;
-                TcLstmPlan* plan = tc_lstm_plan_create(L.w_dev, Gx, Tg, gx_div, Y, wsp->Yb, wsp->ready, B, T, H, h->num_sms, getenv("AVC_LSTM_TM_EXPERIMENT") != nullptr, &why);
-                if (!plan) { rc = fail(h, AVC_ERR_UNSUPPORTED, "tensor-core LSTM plan for %s: %s", L.name.c_str(), why ? why : "?"); return; }
-                h->lplans.push_back(plan);
-            }
-            check(cudaMemsetAsync(wsp->ready, 0, wsp->ready_bytes, s), "memset step counters");
-            int n = 0;
-            check(launch_tc_lstm(h->lplans[lplan_cursor++], s, &n), L.name.c_str());
-            h->launches += n;
-            return;
-        }
         check(cudaMemsetAsync(wsp->cstate, 0, (size_t)2 * B * H * 4, s), "memset c");
         const int ldy = ndir * H;
         for (int step = 0; step < T && ok(); ++step) {
@@ -421,6 +426,39 @@ struct Runner {
     Workspace* wsp = nullptr;
 };
 
+// ---- plan cache (LRU) ----
+void drop_plans(avc_ctx* h, int mode_filter = -1) {      // mode_filter < 0: every entry; 2: the speaker encoder's; 0: the generator's (modes != 2)
+    std::vector<PlanSet*> keep;
+    for (auto* ps : h->plan_cache) {
+        const bool drop = mode_filter < 0 || (mode_filter == 2 ? ps->mode == 2 : ps->mode != 2);
+        if (drop) delete ps; else keep.push_back(ps);
+    }
+    h->plan_cache.swap(keep);
+}
+void drop_plan_set(avc_ctx* h, PlanSet* ps) {
+    for (size_t i = 0; i < h->plan_cache.size(); ++i)
+        if (h->plan_cache[i] == ps) { h->plan_cache.erase(h->plan_cache.begin() + i); break; }
+    delete ps;
+}
+// the entry for (workspace, B, T, mode), created empty (least recently used entry evicted) when absent
+PlanSet* plan_set_for(avc_ctx* h, void* ws, int B, int T, int mode, bool* fresh) {
+    for (auto* ps : h->plan_cache)
+        if (ps->ws == ws && ps->B == B && ps->T == T && ps->mode == mode) { ps->stamp = ++h->plan_clock; *fresh = false; return ps; }
+    if (h->plan_cache.size() >= PLAN_CACHE_ENTRIES) {
+        size_t lru = 0;
+        for (size_t i = 1; i < h->plan_cache.size(); ++i)
+            if (h->plan_cache[i]->stamp < h->plan_cache[lru]->stamp) lru = i;
+        delete h->plan_cache[lru];
+        h->plan_cache.erase(h->plan_cache.begin() + lru);
+    }
+    PlanSet* ps = new PlanSet();
+    ps->ws = ws; ps->B = B; ps->T = T; ps->mode = mode; ps->stamp = ++h->plan_clock;
+    h->plan_cache.push_back(ps);
+    h->plan_builds++;
+    *fresh = true;
+    return ps;
+}
+
 int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int B, int T, float* mel, float* mel_post,
         float* codes, void* workspace, size_t workspace_bytes, void* stream, bool encode_only, bool bn_train = false,
         float* bn_stats = nullptr) {
@@ -434,7 +472,8 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     Workspace w = carve(h, (char*)workspace, B, T);
     if (!workspace || workspace_bytes < w.total || ((uintptr_t)workspace & 255))
         return fail(h, AVC_ERR_WORKSPACE, "workspace must be 256-byte aligned and >= %zu bytes (got %zu)", w.total, workspace_bytes);
-    cudaError_t e = cudaSetDevice(h->device);
+    DeviceGuard guard;
+    cudaError_t e = guard.enter(h->device);
     if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
 
     Runner r{h, (cudaStream_t)stream, B, T};
@@ -445,17 +484,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     for (auto ev : h->prof_events) cudaEventDestroy(ev);
     h->prof_events.clear(); h->prof_cats.clear();
     if (r.use_tc()) {
-        const bool hit = h->plan_ws == workspace && h->plan_B == B && h->plan_T == T && h->plan_mode == mode && !h->plans.empty();
-        if (!hit) {
-            for (auto* p : h->plans) tc_gemm_plan_destroy(p);
-            h->plans.clear();
-            for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
-            h->lplans.clear();
-            for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
-            h->llplans.clear();
-            r.building_plans = true;
-            h->plan_ws = workspace; h->plan_B = B; h->plan_T = T; h->plan_mode = mode;
-        }
+        r.ps = plan_set_for(h, workspace, B, T, mode, &r.building_plans);
     }
 
     const int at = act_type(h), pt = post_type(h);
@@ -511,15 +540,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         r.conv_bn(10, w.actB, pt, CONV_CH, M, T, ACT_NONE, nullptr, DT_F32, 0, mel_post, mel);
     }
     r.mark(AVC_PHASE_COUNT);  // closing marker
-    if (!r.ok() && r.building_plans) {  // do not keep a half-built plan set
-        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
-        h->plans.clear();
-        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
-        h->lplans.clear();
-        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
-        h->llplans.clear();
-        h->plan_ws = nullptr;
-    }
+    if (!r.ok() && r.building_plans && r.ps) drop_plan_set(h, r.ps);   // do not keep a half-built plan set
     return r.rc;
 }
 
@@ -541,9 +562,7 @@ SeWorkspace carve_se(const avc_ctx* h, char* base, int N, int T) {
     w.Yb2 = take(M * SE_H * as);
     w.E = (float*)take((size_t)N * SE_EMB * 4);
     w.lstm.cstate = (float*)take((size_t)2 * N * SE_H * 4);
-    w.lstm.ready_bytes = (size_t)tc_lstm_ready_words(N, T) * 4;
-    w.lstm.ready = (unsigned int*)take(w.lstm.ready_bytes);
-    w.lstm.Yb = take(tc_lstm_tile_bytes(N, T, SE_H));
+    w.lstm.Yb = take(ll_lstm_exchange_bytes(N, T, SE_H));
     w.total = off;
     return w;
 }
@@ -556,7 +575,8 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
     SeWorkspace w = carve_se(h, (char*)workspace, N, T);
     if (!workspace || workspace_bytes < w.total || ((uintptr_t)workspace & 255))
         return fail(h, AVC_ERR_WORKSPACE, "workspace must be 256-byte aligned and >= %zu bytes (got %zu)", w.total, workspace_bytes);
-    cudaError_t e = cudaSetDevice(h->device);
+    DeviceGuard guard;
+    cudaError_t e = guard.enter(h->device);
     if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
 
     Runner r{h, (cudaStream_t)stream, N, T};
@@ -565,17 +585,7 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
     for (auto ev : h->prof_events) cudaEventDestroy(ev);
     h->prof_events.clear(); h->prof_cats.clear();
     if (r.use_tc()) {
-        const bool hit = h->plan_ws == workspace && h->plan_B == N && h->plan_T == T && h->plan_mode == 2 && !h->plans.empty();
-        if (!hit) {
-            for (auto* p : h->plans) tc_gemm_plan_destroy(p);
-            h->plans.clear();
-            for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
-            h->lplans.clear();
-            for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
-            h->llplans.clear();
-            r.building_plans = true;
-            h->plan_ws = workspace; h->plan_B = N; h->plan_T = T; h->plan_mode = 2;
-        }
+        r.ps = plan_set_for(h, workspace, N, T, 2, &r.building_plans);
     }
     const int at = act_type(h);
     const int M = N * T, Kp = round_up(SE_MELS, 16);
@@ -591,15 +601,7 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
     const char* h_last = in + (size_t)(T - 1) * SE_H * dtype_size(at);
     r.gemm(L_SE_LINEAR, h_last, at, T * SE_H, N, 1, ACT_RELU, w.E, DT_F32, SE_EMB);
     r.check(launch_l2norm_rows(w.E, embeds, N, SE_EMB, r.s), "l2 normalise"); h->launches++;
-    if (!r.ok() && r.building_plans) {
-        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
-        h->plans.clear();
-        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
-        h->lplans.clear();
-        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
-        h->llplans.clear();
-        h->plan_ws = nullptr;
-    }
+    if (!r.ok() && r.building_plans && r.ps) drop_plan_set(h, r.ps);
     return r.rc;
 }
 
@@ -610,7 +612,7 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
 // ---------------------------------------------------------------------------------------------
 extern "C" {
 
-int avc_abi_version(void) { return 5; }
+int avc_abi_version(void) { return 6; }
 
 int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision) {
     if (!out || !dims) return fail(nullptr, AVC_ERR_INVALID_ARG, "null out/dims");
@@ -629,12 +631,11 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
     h->force_simt = fs && fs[0] == '1';
     const char* sl = getenv("AVC_SIMT_LSTM");
     h->simt_lstm = sl && sl[0] == '1';
-    const char* li = getenv("AVC_LSTM_IMPL");
-    h->old_lstm = li && li[0] == 't';
     h->gx_f32 = getenv("AVC_GX_F32") != nullptr;
     for (int i = 0; i < L_COUNT; ++i) h->layers[i].name = kLayerNames[i];
     if (device >= 0) {
-        cudaError_t e = cudaSetDevice(device);
+        DeviceGuard guard;
+        cudaError_t e = guard.enter(device);
         cudaDeviceProp prop{};
         if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
         if (e != cudaSuccess) { int rc = fail(nullptr, AVC_ERR_CUDA, "cuda device %d: %s", device, cudaGetErrorString(e)); delete h; return rc; }
@@ -642,7 +643,6 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
         h->num_sms = prop.multiProcessorCount;
         if (precision == AVC_PREC_BF16 && !h->force_simt) {
             const char* why = tc_init();
-            if (!why) why = tc_lstm_init();
             if (!why) why = ll_lstm_init();
             if (why) { int rc = fail(nullptr, AVC_ERR_CUDA, "tensor-core kernel setup: %s", why); delete h; return rc; }
         }
@@ -700,8 +700,10 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
     }
     for (int i = 0; i < N_BN; ++i) L[L_RAW_CONV0 + i].w_type = L[kBnFolded[i]].w_type;
     if (h->device >= 0) {
-        cudaError_t e = cudaSetDevice(h->device);
+        DeviceGuard guard;
+        cudaError_t e = guard.enter(h->device);
         if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+        drop_plans(h, 0);     // cached generator plans point at the old weight buffers
         for (int i = 0; i < L_GEN_COUNT; ++i) {
             int rc = upload_layer(h, L[i]);
             if (rc != AVC_OK) return rc;
@@ -718,13 +720,6 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
                 if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "uploading BatchNorm parameters: %s", cudaGetErrorString(e));
             }
         }
-        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
-        h->plans.clear();
-        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
-        h->lplans.clear();
-        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
-        h->llplans.clear();
-        h->plan_ws = nullptr;
     }
     h->loaded = true;
     return AVC_OK;
@@ -752,6 +747,8 @@ int avc_forward_bn_train(avc_handle h, const float* x, const float* c_org, const
 }
 
 int64_t avc_last_launch_count(avc_handle h) { return h ? h->launches : 0; }
+
+int64_t avc_plan_builds(avc_handle h) { return h ? h->plan_builds : 0; }
 
 int avc_set_profiling(avc_handle h, int enable) {
     if (!h) return AVC_ERR_INVALID_ARG;
@@ -832,22 +829,15 @@ int avc_se_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
     ok = ok && pack_linear(h, L[L_SE_LINEAR], "linear", SE_H, SE_EMB);
     h->raw.clear();
     if (!ok) return AVC_ERR_MISSING_WEIGHT;
-    for (int i = L_SE_L0_IH; i < L_COUNT; ++i) L[i].w_type = h->precision == AVC_PREC_FP32 ? DT_F32 : DT_BF16;
+    for (int i = L_SE_L0_IH; i <= L_SE_LINEAR; ++i) L[i].w_type = h->precision == AVC_PREC_FP32 ? DT_F32 : DT_BF16;
     if (h->device >= 0) {
-        cudaError_t e = cudaSetDevice(h->device);
+        DeviceGuard guard;
+        cudaError_t e = guard.enter(h->device);
         if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
-        for (int i = L_SE_L0_IH; i < L_COUNT; ++i) {
+        drop_plans(h, 2);     // cached speaker-encoder plans point at the old weight buffers
+        for (int i = L_SE_L0_IH; i <= L_SE_LINEAR; ++i) {
             int rc = upload_layer(h, L[i]);
             if (rc != AVC_OK) return rc;
-        }
-        if (h->plan_mode == 2) {   // cached speaker-encoder plans point at the old weight buffers
-            for (auto* p : h->plans) tc_gemm_plan_destroy(p);
-            h->plans.clear();
-            for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
-            h->lplans.clear();
-            for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
-            h->llplans.clear();
-            h->plan_ws = nullptr;
         }
     }
     h->se_loaded = true;
@@ -867,7 +857,8 @@ int avc_se_forward(avc_handle h, const float* partials, int N, int T, float* emb
 int avc_se_reduce(avc_handle h, const float* embeds, const int32_t* offsets, int S, float* speaker_embeds, void* stream) {
     if (!h || !embeds || !offsets || !speaker_embeds || S <= 0) return fail(h, AVC_ERR_INVALID_ARG, "null pointer or S <= 0");
     if (h->device < 0) return fail(h, AVC_ERR_INVALID_ARG, "host-only context (device=-1) cannot run");
-    cudaError_t e = cudaSetDevice(h->device);
+    DeviceGuard guard;
+    cudaError_t e = guard.enter(h->device);
     if (e == cudaSuccess) e = launch_segment_mean_renorm(embeds, offsets, speaker_embeds, S, SE_EMB, (cudaStream_t)stream);
     if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "segment mean: %s", cudaGetErrorString(e));
     return AVC_OK;
@@ -876,7 +867,8 @@ int avc_se_reduce(avc_handle h, const float* embeds, const int32_t* offsets, int
 void avc_destroy(avc_handle h) {
     if (!h) return;
     if (h->device >= 0) {
-        cudaSetDevice(h->device);
+        DeviceGuard guard;
+        guard.enter(h->device);
         for (int i = 0; i < L_COUNT; ++i) {
             if (h->layers[i].w_dev) cudaFree(h->layers[i].w_dev);
             if (h->layers[i].b_dev) cudaFree(h->layers[i].b_dev);
@@ -885,9 +877,7 @@ void avc_destroy(avc_handle h) {
             if (h->bn_gamma_dev[i]) cudaFree(h->bn_gamma_dev[i]);
             if (h->bn_beta_dev[i]) cudaFree(h->bn_beta_dev[i]);
         }
-        for (auto* p : h->plans) tc_gemm_plan_destroy(p);
-        for (auto* p : h->lplans) tc_lstm_plan_destroy(p);
-        for (auto* p : h->llplans) ll_lstm_plan_destroy(p);
+        drop_plans(h);
         for (auto ev : h->prof_events) cudaEventDestroy(ev);
     }
     delete h;

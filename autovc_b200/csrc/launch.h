@@ -2,7 +2,50 @@
 #pragma once
 #include "common.cuh"
 
+#include <cstdlib>
+#include <cstring>
+
+extern char** environ;
+
 namespace avc {
+
+// Launch of a persistent kernel whose CTAs wait on one another (clusters of `cluster_x` CTAs): cooperative by default, so the
+// driver guarantees that the whole grid is co-resident (gang-scheduled).  Profilers that replay kernels (ncu) cannot take a
+// cooperative cluster launch; then - and only after cudaOccupancyMaxActiveClusters has confirmed that the grid fits the
+// machine - the launch is repeated without the attribute.  `*NOCOOP` environment variables / a detected profiler injection
+// skip the cooperative attempt.  reference: none (launch mechanics of this library).
+inline bool profiler_attached() {
+    static const int v = [] {
+        for (char** e = environ; e && *e; ++e)
+            if (!strncmp(*e, "NV_COMPUTE_PROFILER_", 20) || !strncmp(*e, "NV_NSIGHT_INJECTION", 19) || !strncmp(*e, "CUDA_INJECTION64_PATH=", 22))
+                return 1;
+        return 0;
+    }();
+    return v != 0;
+}
+inline cudaError_t launch_persistent(const void* fn, dim3 grid, dim3 block, size_t smem, unsigned cluster_x, void** kargs,
+                                     cudaStream_t s, bool force_nocoop) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster_x; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
+    cfg.attrs = at;
+    if (!force_nocoop && !profiler_attached()) {
+        cfg.numAttrs = 2;
+        cudaError_t e = cudaLaunchKernelExC(&cfg, fn, kargs);
+        if (e == cudaSuccess) return e;
+        (void)cudaGetLastError();      // clear the launch error and fall through to the checked non-cooperative launch
+    }
+    cfg.numAttrs = 1;
+    int clusters = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&clusters, fn, &cfg);
+    if (e != cudaSuccess) return e;
+    const long long need = (long long)grid.x * grid.y * grid.z / (cluster_x ? cluster_x : 1);
+    if (clusters < need) return cudaErrorCooperativeLaunchTooLarge;
+    return cudaLaunchKernelExC(&cfg, fn, kargs);
+}
 
 // simt_kernels.cu
 cudaError_t launch_simt_gemm(const GemmParams& p, cudaStream_t s);
@@ -50,16 +93,6 @@ int tc_gemm_plan_stat_chunks(const TcGemmPlan* plan);
 cudaError_t launch_tc_gemm(const TcGemmPlan* plan, cudaStream_t s, float* out_t, const float* res_t);
 // one-time driver entry point lookup; returns nullptr on success or an error string
 const char* tc_init();
-
-// tc_lstm.cu (persistent weight-stationary LSTM recurrence, tcgen05 + TMA + global step counters)
-struct TcLstmPlan;
-const char* tc_lstm_init();
-size_t tc_lstm_tile_bytes(int B, int T, int H);
-TcLstmPlan* tc_lstm_plan_create(const void* Whh_bf16, const float* Gx, int Tg, int gx_div, void* Y, void* Yb, unsigned int* ready,
-                                int B, int T, int H, int num_sms, bool time_major, const char** err);
-void tc_lstm_plan_destroy(TcLstmPlan* plan);
-int tc_lstm_ready_words(int B, int T);
-cudaError_t launch_tc_lstm(const TcLstmPlan* plan, cudaStream_t s, int* launches);
 
 // ll_lstm.cu (persistent weight-stationary LSTM recurrence, tcgen05; h exchanged through L2 with in-band validity)
 struct LlLstmPlan;

@@ -602,17 +602,10 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
         args.trace = tracing ? d_trace : nullptr;
         if (tracing) cudaMemsetAsync(d_trace, 0, sizeof(long long) * (TRACE_STEPS + 1) * TRACE_PTS, s);
         void* kargs[2] = {(void*)&plan->tmW, (void*)&args};
-        // cooperative launch: CTAs wait on one another's output, so co-residency must be guaranteed
-        cudaLaunchConfig_t cfg{};
-        cfg.gridDim = plan->grids[i]; cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = (size_t)plan->smem_bytes; cfg.stream = s;
-        cudaLaunchAttribute at[2];
-        at[0].id = cudaLaunchAttributeClusterDimension;      // CTA pairs: adjacent unit slices of one batch tile
-        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
-        // AVC_LSTM_NOCOOP: profiling aid (ncu refuses cooperative cluster launches); the grid is sized to be
-        // co-resident either way, the attribute only makes the driver check it
-        cfg.attrs = at; cfg.numAttrs = getenv("AVC_LSTM_NOCOOP") ? 1 : 2;
-        e = cudaLaunchKernelExC(&cfg, kernel_for(plan->nkb, plan->gx_f16, plan->tn), kargs);
+        // CTAs wait on one another's output: cooperative launch (guaranteed co-residency), with the checked non-cooperative
+        // retry of launch_persistent() for profilers (AVC_LSTM_NOCOOP forces it)
+        e = launch_persistent(kernel_for(plan->nkb, plan->gx_f16, plan->tn), plan->grids[i], dim3(NUM_THREADS), (size_t)plan->smem_bytes, 2,
+                              kargs, s, getenv("AVC_LSTM_NOCOOP") != nullptr);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
         if (tracing) {   // debugging aid: synchronous dump of the per-step timeline of CTA (0,0)

@@ -37,6 +37,7 @@
 
 #include "../../include/autovc_b200.h"
 #include "common.cuh"
+#include "launch.h"
 #include "ptx.cuh"
 
 namespace avc {
@@ -894,16 +895,9 @@ int avc_voc_generate(avc_voc_handle h, const float* m_up, const float* aux, int 
     const void* fn = tiles == 1 ? (const void*)voc_generate_kernel<1> : tiles == 2 ? (const void*)voc_generate_kernel<2> : (const void*)voc_generate_kernel<4>;
     a.cs = h->cs;
     a.stages = getenv("AVC_VOC_STAGES") ? std::max(2, std::min(STAGES, atoi(getenv("AVC_VOC_STAGES")))) : STAGES;
-    // cooperative launch: CTAs wait on one another's output, so co-residency must be guaranteed.  AVC_VOC_NOCOOP drops the
-    // attribute for profilers that cannot replay cooperative cluster launches (the grid is sized to be co-resident anyway).
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(VCTAS); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = s;
-    cudaLaunchAttribute at[2];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = (unsigned)h->cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
-    cfg.attrs = at; cfg.numAttrs = getenv("AVC_VOC_NOCOOP") ? 1 : 2;
-    cudaError_t e = cudaLaunchKernelExC(&cfg, fn, kargs);
+    // CTAs wait on one another's output: cooperative launch (guaranteed co-residency), with the checked non-cooperative retry
+    // of launch_persistent() for profilers that cannot replay cooperative cluster launches (AVC_VOC_NOCOOP forces it)
+    cudaError_t e = launch_persistent(fn, dim3(VCTAS), dim3(256), SMEM_BYTES, (unsigned)h->cs, kargs, s, getenv("AVC_VOC_NOCOOP") != nullptr);
     h->launches = 3;
     if (e != cudaSuccess) return voc_fail(h, AVC_ERR_CUDA, "vocoder loop launch failed: %s", cudaGetErrorString(e));
     return AVC_OK;

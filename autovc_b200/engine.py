@@ -186,6 +186,10 @@ class Engine:
     def last_launch_count(self) -> int:
         return int(L.lib().avc_last_launch_count(self._h))
 
+    @property
+    def plan_builds(self) -> int:
+        return int(L.lib().avc_plan_builds(self._h))
+
     def close(self) -> None:
         if self._h:
             L.lib().avc_destroy(self._h)

@@ -21,6 +21,7 @@ from typing import Dict, Optional, Tuple
 import torch
 import torch.nn as nn
 
+from ._weights import PackedWeightsMixin
 from .engine import Engine
 from .synth import CONV_CH, KSIZE, LSTM2_HIDDEN, N_MELS
 
@@ -86,7 +87,7 @@ class Postnet(_ParamOnly):
         self.convolutions = nn.ModuleList(blocks)
 
 
-class AutoEncoder(nn.Module):
+class AutoEncoder(PackedWeightsMixin, nn.Module):
     """B200-native AutoVC generator.
 
     Parameters mirror reference `AutoEncoder.__init__` (`model.py:31-38`; defaults from `utils/hparams.py:17-20`).
@@ -109,21 +110,23 @@ class AutoEncoder(nn.Module):
         self.decoder = Decoder(dim_neck, dim_emb, dim_pre)
         self.postnet = Postnet()
         self.train(False)  # parity contract: eval-mode BatchNorm
+        self._init_tracking()
         self._engines: Dict[Tuple[int, str], Engine] = {}
         self._engine_keys: Dict[Tuple[int, str], Tuple[int, int]] = {}
 
-    # -- weights -----------------------------------------------------------------------------------
-    def _weights_key(self) -> Tuple[int, int]:
-        """(all tensors, all but the BatchNorm running statistics): each changes whenever one of its tensors is modified
-        in place or replaced.  The batch-statistics forward does not read the running statistics, so it only needs the
-        second key to be current (it updates those buffers itself after every call)."""
-        k = p = 0
-        for name, t in self.state_dict(keep_vars=True).items():
-            v = t._version + (t.data_ptr() & 0xFFFFFFF)
-            k = (k * 1000003 + v) & 0xFFFFFFFFFFFF
-            if "running_" not in name and "num_batches_tracked" not in name:
-                p = (p * 1000003 + v) & 0xFFFFFFFFFFFF
-        return k, p
+    # -- weights (change tracking: _weights.PackedWeightsMixin) ----------------------------------------
+    def flatten_params(self) -> torch.Tensor:
+        """reference `AutoEncoder.flatten_params` (`model.py:379-383`): all parameters as one vector."""
+        return torch.cat([p.data.view(-1) for p in self.parameters()], 0)
+
+    def load_flattened_params(self, flattened_params: torch.Tensor) -> None:
+        """reference `load_flattened_params` (`model.py:385-392`; the EMA weights of `learn`, `:275,321`).  Writes
+        through `.data` like the reference and then invalidates the packed copy."""
+        offset = 0
+        for p in self.parameters():
+            p.data.copy_(flattened_params[offset:offset + p.nelement()].view(p.size()))
+            offset += p.nelement()
+        self.invalidate()
 
     def _engine(self, device: torch.device, params_only: bool = False) -> Engine:
         idx = device.index if device.index is not None else torch.cuda.current_device()
@@ -132,7 +135,7 @@ class AutoEncoder(nn.Module):
         if eng is None:
             eng = Engine(self.dims, idx, self.precision)
             self._engines[key] = eng
-            self._engine_keys[key] = (-1, -1)
+            self._engine_keys[key] = (None, None)
         wk = self._weights_key()
         if (self._engine_keys[key][1] != wk[1]) if params_only else (self._engine_keys[key] != wk):
             eng.load_state_dict(self.state_dict())

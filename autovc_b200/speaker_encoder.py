@@ -22,10 +22,11 @@ import numpy as np
 import torch
 import torch.nn as nn
 
+from ._weights import PackedWeightsMixin
 from .engine import Engine
 
 
-class SpeakerEncoder(nn.Module):
+class SpeakerEncoder(PackedWeightsMixin, nn.Module):
     def __init__(self, input_size: int = 40, hidden_size: int = 256, embedding_size: int = 256, num_layers: int = 3,
                  batch_first: bool = True, device=None, verbose: bool = True, precision: str = "bf16"):
         super().__init__()
@@ -42,16 +43,11 @@ class SpeakerEncoder(nn.Module):
         self.lstm = nn.LSTM(input_size=input_size, hidden_size=hidden_size, num_layers=num_layers, batch_first=batch_first)
         self.linear = nn.Linear(in_features=hidden_size, out_features=embedding_size)
         self.train(False)
+        self._init_tracking()
         self._engines: Dict[Tuple[int, str], Engine] = {}
-        self._engine_keys: Dict[Tuple[int, str], int] = {}
+        self._engine_keys: Dict[Tuple[int, str], object] = {}
 
     # -- weights -----------------------------------------------------------------------------------
-    def _weights_key(self) -> int:
-        k = 0
-        for t in self.state_dict(keep_vars=True).values():
-            k = (k * 1000003 + t._version + (t.data_ptr() & 0xFFFFFFF)) & 0xFFFFFFFFFFFF
-        return k
-
     def _engine(self, device: torch.device) -> Engine:
         idx = device.index if device.index is not None else torch.cuda.current_device()
         key = (idx, self.precision)
@@ -59,8 +55,8 @@ class SpeakerEncoder(nn.Module):
         if eng is None:
             eng = Engine((32, 256, 512, 32), idx, self.precision)   # generator dims are unused by the speaker encoder
             self._engines[key] = eng
-            self._engine_keys[key] = -1
-        wk = self._weights_key()
+            self._engine_keys[key] = None
+        wk = self._weights_key()[0]
         if self._engine_keys[key] != wk:
             eng.load_state_dict(self.state_dict(), speaker_encoder=True)
             self._engine_keys[key] = wk

@@ -26,6 +26,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib as L
+from ._weights import PackedWeightsMixin
 from .synth import WAVERNN
 
 HOP = WAVERNN["hop_length"]
@@ -69,7 +70,9 @@ class _ParamsOnly(nn.Module):
             self.register_parameter(k, nn.Parameter(v, requires_grad=False))
 
 
-class WaveRNN(nn.Module):
+class WaveRNN(PackedWeightsMixin, nn.Module):
+    _skip_in_key = ("num_batches_tracked", "step")
+
     def __init__(self, hop_length=WAVERNN["hop_length"], rnn_dims=WAVERNN["rnn_dims"], res_out_dims=WAVERNN["res_out_dims"],
                  feat_dims=WAVERNN["feat_dims"], fc_dims=WAVERNN["fc_dims"], bits=WAVERNN["bits"],
                  upsample_factors=WAVERNN["upsample_factors"], compute_dims=WAVERNN["compute_dims"], pad=WAVERNN["pad"],
@@ -118,19 +121,14 @@ class WaveRNN(nn.Module):
         self.train(False)
         for p in self.parameters():
             p.requires_grad_(False)
+        self._init_tracking()
         self._handles: Dict[int, ctypes.c_void_p] = {}
-        self._keys: Dict[int, int] = {}
+        self._keys: Dict[int, object] = {}
         self.last_launch_count = 0
         self.last_rows = 0
         self.last_steps = 0
 
     # -- weights -----------------------------------------------------------------------------------
-    def _weights_key(self) -> int:
-        k = 0
-        for t in self.state_dict(keep_vars=True).values():
-            k = (k * 1000003 + t._version + (t.data_ptr() & 0xFFFFFFF)) & 0xFFFFFFFFFFFF
-        return k
-
     def _handle(self, device: torch.device) -> ctypes.c_void_p:
         idx = device.index if device.index is not None else torch.cuda.current_device()
         h = self._handles.get(idx)
@@ -140,8 +138,8 @@ class WaveRNN(nn.Module):
             if rc != L.AVC_OK:
                 raise RuntimeError(f"avc_voc_create failed ({rc}): {L.lib().avc_voc_last_error(None).decode()}")
             self._handles[idx] = h
-            self._keys[idx] = -1
-        wk = self._weights_key()
+            self._keys[idx] = None
+        wk = self._weights_key()[0]
         if self._keys[idx] != wk:
             sd = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in self.state_dict().items()
                   if not k.endswith("num_batches_tracked") and k != "step"}

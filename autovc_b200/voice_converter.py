@@ -8,7 +8,8 @@
 * utterances are never padded across different lengths - the reference has no length masking, so padding would change
   the BiLSTM result (SURVEY.md 8e);
 * under `torch.distributed` every rank converts a contiguous block of the work list with replicated weights and no
-  collective on the data path; an optional final `all_gather_object` returns the complete list on every rank.
+  collective on the data path; an optional final tensor all-gather (NCCL over NVLink, one per length bucket) returns
+  the complete list on every rank.
 
 `VoiceConverter` works on mels: inputs are normalised mels `(80, T)`, outputs are `mel_outputs_postnet` `(80, T)` exactly
 as `convert` hands them to the vocoder (`:170,:175`).  `WavVoiceConverter` is the waveform-level `convert`: mel front-end
@@ -62,6 +63,24 @@ def chunk_mel(mel: torch.Tensor, n_frames: int, overlap: float = 0.5) -> torch.T
     return torch.stack([mel[:, s:s + n_frames] for s in starts])
 
 
+def host_rows(rows: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Equal-shaped CPU tensors -> one pinned float32 tensor (len, *shape) for an asynchronous host->device copy.
+    Rows that already are consecutive slices of one pinned float32 tensor are returned as a view of it (no copy);
+    anything else is stacked into pinned staging memory (torch's caching host allocator recycles it)."""
+    first = rows[0]
+    n, shape = len(rows), tuple(first.shape)
+    if first.dtype == torch.float32 and first.is_contiguous() and first.is_pinned():
+        step = first.numel() * 4
+        base, store = first.data_ptr(), first.untyped_storage().data_ptr()
+        if all(r.dtype == torch.float32 and tuple(r.shape) == shape and r.is_contiguous() and r.data_ptr() == base + j * step
+               and r.untyped_storage().data_ptr() == store for j, r in enumerate(rows)):
+            strides = (first.numel(),) + tuple(first.stride())
+            return torch.as_strided(first, (n,) + shape, strides)
+    staged = torch.empty((n,) + shape, dtype=torch.float32, pin_memory=torch.cuda.is_available())
+    torch.stack([r.to(torch.float32) for r in rows], out=staged)
+    return staged
+
+
 class VoiceConverter:
     """Mel-level drop-in for the conversion loop of the reference `VoiceConverter`.
 
@@ -78,11 +97,33 @@ class VoiceConverter:
         self.max_batch = int(max_batch)
         self.speakers: Dict[Hashable, torch.Tensor] = {}
         self.embed_calls = 0
+        self._pipe: Optional["HostPipeline"] = None
 
     # -- speakers ----------------------------------------------------------------------------------
     def learn_speaker(self, key: Hashable, embedding: torch.Tensor) -> None:
         """Register a (mean) speaker embedding under a key, like `SpeakerEncoder.learn_speaker` fills `.speakers`."""
         self.speakers[key] = embedding.detach().to(torch.float32).reshape(-1).cpu()
+
+    def learn_speakers(self, keys: Sequence[Hashable], datas: Sequence[object], embed_many: Optional[Callable] = None) -> int:
+        """Embed every not-yet-known speaker of `keys` ONCE, all of them in one batched call of the d-vector encoder
+        (`embed_many(list of speaker data) -> (n, dim_emb)`, e.g. `SpeakerEncoder.embed_speakers`; default: the
+        converter's per-speaker `embed_speaker`), and cache them like `SpeakerEncoder.speakers` (reference
+        `speaker_encoder/model.py:101,446-460`).  Returns the number of speakers embedded."""
+        todo, seen = [], set()
+        for k, d in zip(keys, datas):
+            if k not in self.speakers and k not in seen and d is not None:
+                seen.add(k); todo.append((k, d))
+        if not todo:
+            return 0
+        if embed_many is not None:
+            embeds = embed_many([d for _, d in todo])
+            self.embed_calls += len(todo)
+            for (k, _), e in zip(todo, embeds.detach().to(torch.float32).cpu()):
+                self.speakers[k] = e.reshape(-1)
+        else:
+            for k, d in todo:
+                self.embedding(k, d)
+        return len(todo)
 
     def embedding(self, ref: SpeakerRef, data: object = None) -> torch.Tensor:
         """Embedding of a speaker: a tensor is used as is, a known key hits the cache (reference `:150-151`), an
@@ -98,19 +139,66 @@ class VoiceConverter:
         return self.speakers[ref]
 
     # -- core: batched forward over a work list ----------------------------------------------------
-    def convert_batch(self, mels: Sequence[torch.Tensor], c_src: Sequence[torch.Tensor], c_trg: Sequence[torch.Tensor]):
-        """[(80,T_i)], [(E,)], [(E,)] -> [mel_outputs_postnet (80,T_i)] in input order.  One forward per
-        (length bucket, chunk of max_batch)."""
-        out: List[Optional[torch.Tensor]] = [None] * len(mels)
-        for T, idx in bucket_by_length([m.shape[-1] for m in mels]).items():
+    def _plan_batches(self, mels: Sequence[torch.Tensor]) -> List[List[int]]:
+        """Index lists, one per forward: (length bucket) x (chunks of max_batch), in first-seen order."""
+        plan = []
+        for _T, idx in bucket_by_length([m.shape[-1] for m in mels]).items():
             for s in range(0, len(idx), self.max_batch):
-                sel = idx[s:s + self.max_batch]
+                plan.append(idx[s:s + self.max_batch])
+        return plan
+
+    def convert_batch(self, mels: Sequence[torch.Tensor], c_src: Sequence[torch.Tensor], c_trg: Sequence[torch.Tensor],
+                      output: str = "device"):
+        """[(80,T_i)], [(E,)], [(E,)] -> [mel_outputs_postnet (80,T_i)] in input order.  One forward per
+        (length bucket, chunk of max_batch).
+
+        Host-resident mels on a CUDA converter go through `HostPipeline`: batch i+1 is staged in pinned memory and copied
+        in while batch i computes and batch i-1's result is copied out.  Mels that are consecutive rows of one pinned
+        tensor (e.g. `Utterance(mel=slab[i])`) are copied straight from it, without staging.
+        `output`: "device" - results stay on the converter's device (stream-ordered, like the reference's tensors);
+        "host" - results are rows of pinned CPU tensors, complete when the call returns."""
+        if output not in ("device", "host"):
+            raise ValueError("output must be 'device' or 'host'")
+        out: List[Optional[torch.Tensor]] = [None] * len(mels)
+        plan = self._plan_batches(mels)
+        if not plan:
+            return out
+        pipelined = self.device.type == "cuda" and all(not m.is_cuda for m in mels)
+        if not pipelined:
+            for sel in plan:
                 x = torch.stack([mels[i] for i in sel]).to(self.device, torch.float32)
                 co = torch.stack([c_src[i] for i in sel]).to(self.device, torch.float32)
                 ct = torch.stack([c_trg[i] for i in sel]).to(self.device, torch.float32)
                 _, post, _ = self.AE(x, co, ct)
+                if output == "host":
+                    post = post.cpu()
                 for j, i in enumerate(sel):
                     out[i] = post[j]
+            return out
+
+        if self._pipe is None:
+            self._pipe = HostPipeline(self.AE, self.device)
+
+        class _Staged:      # batch i is staged when the pipeline enqueues its copy, i.e. while batch i-1 computes
+            def __len__(_s):
+                return len(plan)
+
+            def __getitem__(_s, i):
+                sel = plan[i]
+                return (host_rows([mels[k] for k in sel]), host_rows([c_src[k] for k in sel]), host_rows([c_trg[k] for k in sel]))
+
+        if output == "host":
+            slabs = [torch.empty((len(sel),) + tuple(mels[sel[0]].shape), dtype=torch.float32, pin_memory=True) for sel in plan]
+            self._pipe.run(_Staged(), [(None, slab, None) for slab in slabs])
+            self._pipe.d2h_stream.synchronize()
+            for sel, slab in zip(plan, slabs):
+                for j, i in enumerate(sel):
+                    out[i] = slab[j]
+        else:
+            def keep(bi, res):
+                for j, i in enumerate(plan[bi]):
+                    out[i] = res[1][j]
+            self._pipe.run(_Staged(), None, on_result=keep)
         return out
 
     # -- reference-shaped API -----------------------------------------------------------------------
@@ -141,10 +229,10 @@ class VoiceConverter:
 
     def convert_multiple(self, sources: Sequence[Utterance], targets: Sequence[Union[Utterance, Hashable]],
                          match_method: str = "all_combinations", bidirectional: bool = False,
-                         distributed: bool = False, gather: bool = True) -> List[Optional[torch.Tensor]]:
+                         distributed: bool = False, gather: bool = True, output: str = "device") -> List[Optional[torch.Tensor]]:
         """reference `convert_multiple` (`:346-398`) as batched work: same pairing and output order, but speakers are
         embedded once each, pairs are bucketed by length, and with `distributed` the pair list is split in contiguous
-        blocks over the ranks (results of other ranks are `None` unless `gather`)."""
+        blocks over the ranks (results of other ranks are `None` unless `gather`).  `output` as in `convert_batch`."""
         pairs: List[Tuple[Utterance, SpeakerRef, object]] = []
         for si, ti in self.match(sources, targets, match_method):
             tgt = targets[ti]
@@ -167,18 +255,45 @@ class VoiceConverter:
         mels = [pairs[i][0].mel for i in mine]
         c_s = [self.embedding(pairs[i][0].speaker, pairs[i][0].speaker_data) for i in mine]
         c_t = [self.embedding(pairs[i][1], pairs[i][2]) for i in mine]
-        local = self.convert_batch(mels, c_s, c_t)
+        local = self.convert_batch(mels, c_s, c_t, output=output)
         results: List[Optional[torch.Tensor]] = [None] * len(pairs)
         for i, r in zip(mine, local):
             results[i] = r
         if distributed and gather and world > 1:
-            import torch.distributed as dist
-            blocks: List[object] = [None] * world
-            dist.all_gather_object(blocks, [r.cpu() for r in local])     # off the hot path (optional gather)
-            for rk, block in enumerate(blocks):
-                for i, r in zip(shard_range(len(pairs), rk, world), block):
-                    results[i] = r
+            self._gather(results, [p[0].mel.shape for p in pairs], local, world, output)
         return results
+
+    def _gather(self, results: List[Optional[torch.Tensor]], shapes: Sequence[Tuple[int, ...]], local: Sequence[torch.Tensor],
+                world: int, output: str) -> None:
+        """Optional final output gather (off the hot path): one `all_gather_into_tensor` per length bucket
+        over the job's backend - NCCL over NVLink for CUDA tensors.  Every rank knows the whole pair list, so the
+        per-rank row counts of each bucket are computed locally and no size exchange is needed; blocks are padded to the
+        largest rank's count (the contiguous sharding leaves them within one row of each other)."""
+        import torch.distributed as dist
+        n = len(shapes)
+        on_cuda = dist.get_backend() == "nccl"
+        dev = self.device if on_cuda else torch.device("cpu")
+        by_rank = [list(shard_range(n, rk, world)) for rk in range(world)]
+        me = dist.get_rank()
+        local_of = {i: r for i, r in zip(by_rank[me], local)}
+        for shape in sorted({tuple(sh) for sh in shapes}):          # same bucket order on every rank
+            rows = [[i for i in blk if tuple(shapes[i]) == shape] for blk in by_rank]
+            cap = max(len(r) for r in rows)
+            if cap == 0:
+                continue
+            send = torch.zeros((cap,) + shape, dtype=torch.float32, device=dev)
+            if rows[me]:
+                send[:len(rows[me])] = torch.stack([local_of[i].to(dev) for i in rows[me]])
+            recv = torch.empty((world * cap,) + shape, dtype=torch.float32, device=dev)     # rank blocks concatenated along dim 0
+            dist.all_gather_into_tensor(recv, send)
+            if output == "host" and recv.is_cuda:
+                recv = recv.cpu()
+            recv = recv.view((world, cap) + shape)
+            for rk, idx in enumerate(rows):
+                if rk == me:
+                    continue
+                for j, i in enumerate(idx):
+                    results[i] = recv[rk, j]
 
 
 class WavVoiceConverter:
@@ -269,13 +384,18 @@ class WavVoiceConverter:
 
 class HostPipeline:
     """Throughput path for host-resident batches: step i+1's host->device copy and step i-1's device->host copy run on
-    a copy stream while step i computes, with double-buffered device inputs/outputs and pinned host outputs.
-    The generator call itself is the unchanged public `AutoEncoder.forward`."""
+    two copy streams (one per direction: the B200's copy engines work independently) while step i computes, with
+    double-buffered device inputs/outputs and pinned host outputs.  The generator call itself is the unchanged public
+    `AutoEncoder.forward`.
+
+    One pipeline drives one `AutoEncoder` from one host thread; the engine behind the module owns one workspace, so two
+    pipelines (or two streams) must not run the same module concurrently."""
 
     def __init__(self, auto_encoder, device: torch.device):
         self.AE = auto_encoder
         self.device = torch.device(device)
-        self.copy_stream = torch.cuda.Stream(self.device)
+        self.h2d_stream = torch.cuda.Stream(self.device)
+        self.d2h_stream = torch.cuda.Stream(self.device)
         self._dev_in = [None, None]
         self._dev_out = [None, None]
         import inspect
@@ -284,11 +404,16 @@ class HostPipeline:
         except (TypeError, ValueError):
             self._supports_out = False
 
-    def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]], outputs: Sequence[Tuple[torch.Tensor, ...]]):
-        """`batches`: pinned host (x, c_org, c_trg); `outputs`: per batch pinned host (mel, mel_post, codes) to fill.
-        Returns after everything is enqueued; the caller synchronises."""
+    def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]],
+            outputs: Optional[Sequence[Tuple[Optional[torch.Tensor], ...]]] = None,
+            on_result: Optional[Callable[[int, Tuple[torch.Tensor, ...]], None]] = None):
+        """`batches`: pinned host (x, c_org, c_trg); `outputs`: per batch pinned host (mel, mel_post, codes) to fill - an
+        entry that is None is not copied back.  `on_result(i, (mel, mel_post, codes))` (device tensors, enqueued on the
+        compute stream) is for callers that keep results on the device: the step then gets fresh output tensors instead
+        of the pipeline's reusable slots.  Returns after everything is enqueued; the caller synchronises."""
         compute = torch.cuda.current_stream(self.device)
-        batches = list(batches)
+        if not hasattr(batches, "__getitem__"):
+            batches = list(batches)     # a sequence is indexed lazily: batch i is first touched when its copy is enqueued
         n = len(batches)
         if n == 0:
             return
@@ -296,18 +421,21 @@ class HostPipeline:
         in_ready = [torch.cuda.Event(), torch.cuda.Event()]
         out_done = [torch.cuda.Event(), torch.cuda.Event()]
         comp_done = [torch.cuda.Event(), torch.cuda.Event()]
+        reuse_out = on_result is None and self._supports_out
 
         def h2d(i):
-            with torch.cuda.stream(self.copy_stream):
+            with torch.cuda.stream(self.h2d_stream):
                 if i >= 2:
-                    self.copy_stream.wait_event(comp_done[i % 2])     # the slot's previous inputs have been consumed
-                slot = dev_in[i % 2]
-                if slot is not None and all(d.shape == t.shape for d, t in zip(slot, batches[i])):
-                    for d, t in zip(slot, batches[i]):                 # steady state: reuse the slot's device buffers
+                    self.h2d_stream.wait_event(comp_done[i % 2])     # the slot's previous inputs have been consumed
+                slot, host = dev_in[i % 2], batches[i]
+                if slot is not None and all(d.shape == t.shape for d, t in zip(slot, host)):
+                    for d, t in zip(slot, host):                       # steady state: reuse the slot's device buffers
                         d.copy_(t, non_blocking=True)
                 else:
-                    dev_in[i % 2] = tuple(t.to(self.device, non_blocking=True) for t in batches[i])
-                in_ready[i % 2].record(self.copy_stream)
+                    dev_in[i % 2] = tuple(t.to(self.device, non_blocking=True) for t in host)
+                    for t in dev_in[i % 2]:
+                        t.record_stream(compute)
+                in_ready[i % 2].record(self.h2d_stream)
 
         h2d(0)
         for i in range(n):
@@ -315,22 +443,27 @@ class HostPipeline:
                 h2d(i + 1)
             compute.wait_event(in_ready[i % 2])
             slot_out = dev_out[i % 2]
-            if slot_out is not None and slot_out[0].shape == dev_in[i % 2][0].shape and self._supports_out:
-                compute.wait_event(out_done[i % 2])                    # the slot's previous results have left the device
-                res = self.AE(*dev_in[i % 2], out=slot_out)           # steady state: no allocation on either stream
+            if reuse_out and slot_out is not None and slot_out[0].shape == dev_in[i % 2][0].shape:
+                if i >= 2:
+                    compute.wait_event(out_done[i % 2])                # the slot's previous results have left the device
+                res = self.AE(*dev_in[i % 2], out=slot_out)           # steady state: no allocation on any stream
             else:
-                res = self.AE(*dev_in[i % 2])
-                dev_out[i % 2] = tuple(res)
-            for t in dev_in[i % 2]:
-                t.record_stream(compute)
+                res = tuple(self.AE(*dev_in[i % 2]))
+                if reuse_out:
+                    dev_out[i % 2] = res
             comp_done[i % 2].record(compute)
-            with torch.cuda.stream(self.copy_stream):
-                self.copy_stream.wait_event(comp_done[i % 2])
-                for dst, src in zip(outputs[i], res):
-                    dst.copy_(src, non_blocking=True)
-                out_done[i % 2].record(self.copy_stream)
-            for t in res:
-                t.record_stream(self.copy_stream)
-        compute.wait_event(out_done[(n - 1) % 2])
-        if n > 1:
-            compute.wait_event(out_done[(n - 2) % 2])
+            if on_result is not None:
+                on_result(i, res)
+            if outputs is not None:
+                with torch.cuda.stream(self.d2h_stream):
+                    self.d2h_stream.wait_event(comp_done[i % 2])
+                    for dst, src in zip(outputs[i], res):
+                        if dst is not None:
+                            dst.copy_(src, non_blocking=True)
+                    out_done[i % 2].record(self.d2h_stream)
+                for t in res:
+                    t.record_stream(self.d2h_stream)
+        if outputs is not None:
+            compute.wait_event(out_done[(n - 1) % 2])
+            if n > 1:
+                compute.wait_event(out_done[(n - 2) % 2])

@@ -147,41 +147,126 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
-def time_oracle(batch: int, frames: int, steps: int, warmup: int):
-    """The reference algorithm (oracle port, torch CPU fp32) on the host cores: frames/s."""
-    from oracle import autovc_oracle as O
+def _reference_module(device: str = "cpu"):
+    """The UNMODIFIED reference `AutoEncoder` (reference autovc/auto_encoder/model.py:27), `.eval()`, seeded weights, on
+    `device`; None when neither /root/reference nor the staged copy oracle/_ref is reachable."""
+    try:
+        from oracle.ref_loader import import_reference
+        AutoEncoder, _SE, root = import_reference(prefer_staged=True)
+    except Exception as exc:      # noqa: BLE001 - reported in the JSON line
+        return None, f"{type(exc).__name__}: {exc}"
+    from autovc_b200.synth import synth_state_dict
+    model = AutoEncoder(device=device, verbose=False)
+    model.load_state_dict(synth_state_dict(0))
+    model.eval()
+    return model.to(device), root
+
+
+def time_cpu_reference(batch: int, frames: int, steps: int, warmup: int, budget_s: float = 0.0):
+    """frames/s of the reference forward on the host cores: the unmodified reference module (kind "reference") when it is
+    reachable, else the oracle port of its algorithm (kind "port").  `budget_s` > 0 shrinks the per-step sample (fewer
+    utterances of the same batch) when a first probe step says the full batch would not fit the budget."""
     from autovc_b200.synth import synth_inputs, synth_state_dict
     torch.set_num_threads(os.cpu_count() or 1)
-    sd = synth_state_dict(0)
+    model, where = _reference_module("cpu")
     x, c_org, c_trg = synth_inputs(batch, frames, seed=1234)
+    if model is not None:
+        kind = "reference"
+
+        def step(n):
+            with torch.no_grad():
+                model(x[:n], c_org[:n], c_trg[:n])
+    else:
+        from oracle import autovc_oracle as O
+        sd = synth_state_dict(0)
+        kind = "port"
+
+        def step(n):
+            O.generator_forward(sd, x[:n], c_org[:n], c_trg[:n])
+    n = batch
+    t0 = time.perf_counter()
+    step(min(batch, 16))                                   # probe (also the first warm-up: thread pools, allocator)
+    probe = (time.perf_counter() - t0) * batch / min(batch, 16)
+    if budget_s > 0 and probe * (steps + warmup) > budget_s:
+        n = max(16, int(batch * budget_s / (probe * (steps + warmup))) // 16 * 16)
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        O.generator_forward(sd, x, c_org, c_trg)
+        step(n)
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
     total = sum(times)
-    return batch * frames * len(times) / total, total / len(times) * 1e3, torch.get_num_threads()
+    sample = (f"{n} of the {batch} utterances x {frames} frames per step, {len(times)} timed steps; "
+              + ("the unmodified reference AutoEncoder.eval() under no_grad (torch CPU fp32, all host threads), imported from " + str(where)
+                 if kind == "reference" else f"oracle port of the reference algorithm (torch CPU fp32; reference module unavailable: {where})"))
+    return {"value": n * frames * len(times) / total, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": kind,
+            "sample": sample, "ms_per_step": total / len(times) * 1e3, "utterances_per_step": n}
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample_b = args.cpu_sample_batch
-    fps, ms, cores = time_oracle(sample_b, args.frames, args.steps, args.warmup)
-    sample = f"{sample_b} of the {args.batch} utterances x {args.frames} frames per step (oracle port of the reference algorithm, torch CPU fp32, all host threads)"
+    # the whole K + W run is bounded to ~6 minutes of host time; on the B200 hosts the full batch fits (about 3 s per step)
+    r = time_cpu_reference(args.batch, args.frames, args.steps, args.warmup, budget_s=360.0)
+    fps = r["value"]
     line = {
         "impl": "reference", "metric": "generator_fwd_mel_frames_per_s", "value": fps, "unit": "frames/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"config2: B={args.batch} x T={args.frames} x 80 mel, dims 32/256/512/32, seeded random-init", "sample": sample},
-        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": f"config2: B={args.batch} x T={args.frames} x 80 mel per GPU, dims 32/256/512/32, seeded random-init weights",
+                   "sample": r["sample"], "same_config": r["utterances_per_step"] == args.batch},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+def gpu_eager_baseline(dev, B, T, x, c_org, c_trg):
+    """The same-box bar: the unmodified reference module `.eval().cuda()` through
+    PyTorch eager + cuDNN/cuBLAS on this B200 - fp32 with TF32 off, and under autocast(bfloat16) - at config 2 and at
+    B = 1.  Returns milliseconds per forward (CUDA events, median)."""
+    model, where = _reference_module("cpu")
+    if model is None:
+        return {"unavailable": where}
+    model = model.to(dev)
+    model.device = dev
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+    def timed(fn, warm, reps):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(reps):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); fn(); e.record(); e.synchronize()
+            ts.append(s.elapsed_time(e))
+        return statistics.median(ts)
+
+    out = {"module": f"unmodified reference AutoEncoder.eval().cuda() from {where}, torch {torch.__version__} eager (cuDNN LSTM/conv)",
+           "config": f"B={B} x T={T}"}
+    try:
+        with torch.no_grad():
+            x1, co1, ct1 = x[:1].contiguous(), c_org[:1].contiguous(), c_trg[:1].contiguous()
+            out["fp32_ms"] = timed(lambda: model(x, c_org, c_trg), 3, 10)
+            out["b1_fp32_ms"] = timed(lambda: model(x1, co1, ct1), 5, 30)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out["bf16_ms"] = timed(lambda: model(x, c_org, c_trg), 3, 10)
+                out["b1_bf16_ms"] = timed(lambda: model(x1, co1, ct1), 5, 30)
+            out["fp32_frames_per_s"] = B * T / (out["fp32_ms"] * 1e-3)
+            out["bf16_frames_per_s"] = B * T / (out["bf16_ms"] * 1e-3)
+            out["b1_ms"] = min(out["b1_fp32_ms"], out["b1_bf16_ms"])
+    except Exception as exc:      # noqa: BLE001
+        out["error"] = f"{type(exc).__name__}: {exc}"
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+        del model
+        torch.cuda.empty_cache()
+    return out
 
 
 def main():
@@ -193,8 +278,8 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="utterances per GPU per step (config 2: 256)")
     ap.add_argument("--frames", type=int, default=128)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--cpu-sample-batch", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the extra configs (c3/c4/c5/b1) and the cuDNN-eager baseline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -204,6 +289,7 @@ def main():
 
     import autovc_b200
     from autovc_b200.synth import synth_inputs, synth_state_dict
+    from autovc_b200.voice_converter import HostPipeline, Utterance, VoiceConverter
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -217,8 +303,9 @@ def main():
     dev = torch.device("cuda", local_rank)
     B, T, K, W = args.batch, args.frames, args.steps, args.warmup
 
+    sd = synth_state_dict(0)
     model = autovc_b200.AutoEncoder(device=dev, verbose=False, precision=args.precision)
-    model.load_state_dict(synth_state_dict(0))
+    model.load_state_dict(sd)
     x_h, co_h, ct_h = synth_inputs(B, T, seed=1234 + rank)
     x_h, co_h, ct_h = x_h.pin_memory(), co_h.pin_memory(), ct_h.pin_memory()
     x, c_org, c_trg = x_h.to(dev), co_h.to(dev), ct_h.to(dev)
@@ -230,6 +317,28 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    def max_over_ranks(*vals):
+        t = torch.tensor(vals, dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t]
+
+    def timed_steps(fn, warm, steps, flush_l2=True):
+        """Sum of the device time (CUDA events on the launching stream) of `steps` calls of fn, bracketed by barriers."""
+        for _ in range(warm):
+            fn()
+        ss = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        es = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        barrier()
+        for i in range(steps):
+            if flush_l2:
+                flush.zero_()                  # evict L2 between timed iterations (not timed)
+            ss[i].record()
+            fn()
+            es[i].record()
+        barrier()
+        return sum(s.elapsed_time(e) for s, e in zip(ss, es))
+
     # ---- warm-up (also builds the engine, packs weights, creates tensor maps) ----
     for _ in range(W):
         model(x, c_org, c_trg)
@@ -238,76 +347,154 @@ def main():
 
     # ---- device-timed region: inputs resident in HBM ----
     sampler = ClockSampler(local_rank)
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     barrier()
     sampler.start()
     wall0 = time.perf_counter()
-    for i in range(K):
-        flush.zero_()                      # evict L2 between timed iterations (not timed)
-        starts[i].record()
-        model(x, c_org, c_trg)
-        ends[i].record()
-    barrier()
+    dev_ms = timed_steps(lambda: model(x, c_org, c_trg), 0, K)
     wall = time.perf_counter() - wall0
     clocks = sampler.stop()
-    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
 
     # ---- end-to-end through the public API with HOST buffers (pinned), copies inside the timed region ----
-    mel_h = torch.empty(B, 80, T, dtype=torch.float32).pin_memory()
-    post_h = torch.empty(B, 80, T, dtype=torch.float32).pin_memory()
     n_codes = 32 * (T // 32 + (T + 31) // 32)
-    codes_h = torch.empty(B, n_codes, dtype=torch.float32).pin_memory()
 
-    # HostPipeline (autovc_b200/voice_converter.py): H2D of step i+1 and D2H of step i-1 ride a copy stream while
-    # step i computes; every step still copies its own inputs in and all three outputs out inside the timed region
-    from autovc_b200.voice_converter import HostPipeline
-    pipe = HostPipeline(model, dev)
-    host_in = [(x_h, co_h, ct_h)] * K
-    host_out = [(mel_h, post_h, codes_h)] * K
-    pipe.run(host_in[:max(2, min(K, 6))], host_out[:max(2, min(K, 6))])   # untimed: fills the allocator's pools for both streams
-    barrier()
-    e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    flush.zero_()
-    barrier()
-    e_start.record()
-    pipe.run(host_in, host_out)
-    e_end.record()
-    barrier()
-    e2e_ms = e_start.elapsed_time(e_end)
+    def pinned_out(b, t):
+        return (torch.empty(b, 80, t, dtype=torch.float32).pin_memory(), torch.empty(b, 80, t, dtype=torch.float32).pin_memory(),
+                torch.empty(b, 32 * (t // 32 + (t + 31) // 32), dtype=torch.float32).pin_memory())
+
+    def e2e_pipeline(mdl, host_in, host_out, steps):
+        """HostPipeline (autovc_b200/voice_converter.py): H2D of step i+1 and D2H of step i-1 ride two copy streams while
+        step i computes; every step copies its own inputs in and all three outputs out inside the timed region."""
+        pipe = HostPipeline(mdl, dev)
+        ins, outs = [host_in] * steps, [host_out] * steps
+        pipe.run(ins[:max(2, min(steps, 6))], outs[:max(2, min(steps, 6))])   # untimed: fills the allocator's pools of the streams
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        flush.zero_()
+        barrier()
+        e0.record()
+        pipe.run(ins, outs)
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1)
+
+    host_out = pinned_out(B, T)
+    e2e_ms = e2e_pipeline(model, (x_h, co_h, ct_h), host_out, K)
     h2d = x_h.numel() * 4 + co_h.numel() * 4 + ct_h.numel() * 4
-    d2h = mel_h.numel() * 4 + post_h.numel() * 4 + codes_h.numel() * 4
+    d2h = sum(t.numel() * 4 for t in host_out)
 
     # ---- per-phase device time (CUDA events inside the library, same stream) for the roofline ----
-    eng.set_profiling(True)
-    phase_ms = {}
-    PROF_STEPS = min(K, 5)
-    for _ in range(PROF_STEPS):
-        flush.zero_()
-        model(x, c_org, c_trg)
-        for k, v in eng.profile().items():
-            phase_ms[k] = phase_ms.get(k, 0.0) + v / PROF_STEPS
-    eng.set_profiling(False)
+    def phases(mdl, inputs, reps):
+        e = mdl._engine(dev)
+        e.set_profiling(True)
+        acc = {}
+        for _ in range(reps):
+            flush.zero_()
+            mdl(*inputs)
+            for k, v in e.profile().items():
+                acc[k] = acc.get(k, 0.0) + v / reps
+        e.set_profiling(False)
+        return {k: round(v, 4) for k, v in acc.items()}
+
+    phase_ms = phases(model, (x, c_org, c_trg), min(K, 5))
 
     # ---- p50 latency of a single 128-frame utterance (B=1) ----
-    x1, co1, ct1 = x[:1].contiguous(), c_org[:1].contiguous(), c_trg[:1].contiguous()
-    for _ in range(3):
-        model(x1, co1, ct1)
-    lat = []
-    for _ in range(30):
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        model(x1, co1, ct1)
-        e.record()
-        e.synchronize()
-        lat.append(s.elapsed_time(e))
-    lat_p50 = statistics.median(lat)
+    def p50(fn, warm, reps):
+        for _ in range(warm):
+            fn()
+        lat = []
+        for _ in range(reps):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); fn(); e.record(); e.synchronize()
+            lat.append(s.elapsed_time(e))
+        return statistics.median(lat)
 
-    # ---- reduce over ranks (max time) ----
-    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    x1, co1, ct1 = x[:1].contiguous(), c_org[:1].contiguous(), c_trg[:1].contiguous()
+    lat_p50 = p50(lambda: model(x1, co1, ct1), 3, 50)
+
+    dev_ms, e2e_ms = max_over_ranks(dev_ms, e2e_ms)
+
+    # ---- the other BASELINE.json configs, same process, a few steps each (device events, max over ranks) ----
+    configs = {}
+    if not args.no_configs and args.precision == "bf16":
+        # latency split at B = 1
+        configs["b1"] = {"workload": "B=1 x T=128 (one utterance)", "p50_ms": lat_p50, "phase_ms": phases(model, (x1, co1, ct1), 5)}
+
+        # C3: long-utterance LSTM stress, B = 64 x T = 1024 (4097 dependent recurrence steps)
+        B3, T3, K3 = 64, 1024, 5
+        x3_h, co3_h, ct3_h = (t.pin_memory() for t in synth_inputs(B3, T3, seed=77 + rank))
+        x3, co3, ct3 = x3_h.to(dev), co3_h.to(dev), ct3_h.to(dev)
+        ms3 = timed_steps(lambda: model(x3, co3, ct3), 2, K3)
+        ph3 = phases(model, (x3, co3, ct3), 2)
+        e3 = e2e_pipeline(model, (x3_h, co3_h, ct3_h), pinned_out(B3, T3), K3)
+        ms3, e3 = max_over_ranks(ms3, e3)
+        configs["c3"] = {"workload": f"config3: B={B3} x T={T3} per GPU", "steps": K3, "ms": ms3 / K3,
+                         "value": world * B3 * T3 * K3 / (ms3 * 1e-3), "unit": "frames/s", "phase_ms": ph3,
+                         "e2e": {"value": world * B3 * T3 * K3 / (e3 * 1e-3), "unit": "frames/s"}}
+        del x3, co3, ct3, x3_h
+
+        # C5: training-shape forward pair (reference model.py:306 then :201), 256 utterances per GPU
+        def pair(mdl):
+            _mel, post, _codes = mdl(x, c_org, c_org)
+            mdl(post, c_org, None)
+        K5 = 5
+        ms5 = timed_steps(lambda: pair(model), 2, K5)
+        tm = autovc_b200.AutoEncoder(device=dev, verbose=False, precision=args.precision, batch_stat_bn=True)
+        tm.load_state_dict(sd)
+        tm.train()
+        ms5t = timed_steps(lambda: pair(tm), 2, K5)
+        e5 = e2e_pipeline(model, (x_h, co_h, co_h), host_out, K5)     # pass 1 from / to host buffers (the pair's second pass stays on the device)
+        ms5, ms5t, e5 = max_over_ranks(ms5, ms5t, e5)
+        configs["c5"] = {"workload": f"config5: forward(x,c,c) + forward(mel_post,c,None), B={B} x T={T} per GPU (2048 over 8 GPUs)",
+                         "steps": K5, "ms": ms5 / K5, "value": world * B * T * K5 / (ms5 * 1e-3), "unit": "frames/s",
+                         "batch_stat_bn": {"ms": ms5t / K5, "value": world * B * T * K5 / (ms5t * 1e-3)},
+                         "e2e": {"value": world * B * T * K5 / (e5 * 1e-3), "unit": "frames/s", "note": "pass 1 through HostPipeline"}}
+        del tm
+
+        # C4: VoiceConverter.convert_multiple, 4096 utterances x T=128 over all ranks, 64 speakers, the d-vector encoder
+        # once per speaker; sources are rows of pinned HOST memory, results come back to pinned host memory
+        from autovc_b200.synth import synth_speaker_encoder
+        N4, S4, T4 = 4096, 64, 128
+        per = (N4 + world - 1) // world
+        lo, hi = min(N4, rank * per), min(N4, (rank + 1) * per)
+        se_sd, _parts = synth_speaker_encoder(5)
+        se = autovc_b200.SpeakerEncoder(device=dev, verbose=False)
+        se.load_state_dict(se_sd)
+        g = torch.Generator().manual_seed(4242)
+        partials = [torch.randn(8, 160, 40, generator=g) for _ in range(S4)]          # SURVEY 8d: [8,160,40] N(0,1)-derived partials per speaker
+        slab = torch.rand(hi - lo, 80, T4, generator=torch.Generator().manual_seed(99 + rank)).pin_memory()
+        dummy = torch.zeros(80, 1)
+        # every rank builds the same work list; only its own block carries real mels (the other ranks' rows are never touched)
+        srcs = [Utterance(slab[i - lo] if lo <= i < hi else dummy, f"spk{i * S4 // N4}", partials[i * S4 // N4]) for i in range(N4)]
+        trgs = [Utterance(dummy, f"spk{(i * S4 // N4 + 1) % S4}", partials[(i * S4 // N4 + 1) % S4]) for i in range(N4)]
+        vc = VoiceConverter(model, embed_speaker=se.as_embed_fn(), device=dev, max_batch=B)
+        mine_keys = [u.speaker for u in srcs[lo:hi]] + [u.speaker for u in trgs[lo:hi]]
+        mine_data = [u.speaker_data for u in srcs[lo:hi]] + [u.speaker_data for u in trgs[lo:hi]]
+        vc.learn_speakers(mine_keys[:1], mine_data[:1], embed_many=se.embed_speakers)    # warm-up of the speaker-encoder path
+        vc.speakers.clear()
+        vc.embed_calls = 0
+        barrier()
+        a0, a1, s1, s2 = (torch.cuda.Event(enable_timing=True) for _ in range(4))
+        a0.record()
+        n_emb = vc.learn_speakers(mine_keys, mine_data, embed_many=se.embed_speakers)     # ONE batched call, once per speaker
+        a1.record()
+        vc.convert_multiple(srcs, trgs, match_method="align", distributed=world > 1, gather=False, output="host")   # warm-up pass
+        barrier()
+        flush.zero_()
+        barrier()
+        s1.record()
+        res = vc.convert_multiple(srcs, trgs, match_method="align", distributed=world > 1, gather=False, output="host")
+        s2.record()
+        barrier()
+        assert sum(r is not None for r in res) == hi - lo and vc.embed_calls == n_emb
+        se_ms, c4_ms = max_over_ranks(a0.elapsed_time(a1), s1.elapsed_time(s2))
+        configs["c4"] = {"workload": f"config4: VoiceConverter.convert_multiple, {N4} utterances x T={T4} in total ({hi - lo} per rank), {S4} speakers, "
+                                     "pinned host mels in, pinned host mel_outputs_postnet out (the call is end to end by construction)",
+                         "ms": c4_ms, "value": N4 * T4 / (c4_ms * 1e-3), "unit": "frames/s",
+                         "e2e": {"value": N4 * T4 / (c4_ms * 1e-3), "unit": "frames/s",
+                                 "h2d_bytes": (hi - lo) * (80 * T4 + 512) * 4, "d2h_bytes": (hi - lo) * 80 * T4 * 4},
+                         "speaker_encoder": {"ms": se_ms, "speakers_per_rank": n_emb, "partials_per_speaker": 8,
+                                             "note": "all speakers of a rank in one batched SpeakerEncoder.embed_speakers call, outside the convert timing"}}
+        del slab, srcs, trgs, res
 
     if rank == 0:
         peaks, peak_src = load_peaks()
@@ -318,14 +505,17 @@ def main():
         dom_flops = 2.0 * MAC_PER_FRAME[dom] * B * T
         achieved = dom_flops / (phase_ms[dom] * 1e-3) / 1e12 if phase_ms[dom] > 0 else 0.0
         peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+        burst = float(peaks.get("bf16_tflops", peak))
         # DRAM bytes of the dominant phase's launches from the committed ncu --set full capture (same config), or null
         traffic = None
-        try:
-            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_ncu_traffic.json")))
-            if (B, T) == (256, 128) and args.precision == "bf16":
-                traffic = tj["bytes_per_step"].get(dom)
-        except Exception:
-            traffic = None
+        for name in ("r2_ncu_traffic.json", "r1_ncu_traffic.json"):
+            try:
+                tj = json.load(open(os.path.join(ROOT, "profiles", name)))
+                if (B, T) == (256, 128) and args.precision == "bf16":
+                    traffic = tj["bytes_per_step"].get(dom)
+                break
+            except Exception:
+                continue
         line = {
             "metric": "generator_fwd_mel_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak",
@@ -333,23 +523,28 @@ def main():
             "config": {"workload": f"config2: B={B} x T={T} x 80 mel per GPU, dims 32/256/512/32, seeded random-init weights",
                        "l2": "256 MB flush written between timed iterations (excluded from the timing)",
                        "parallelism": f"replicas x{world}, no data-path collective",
-                       "e2e": "HostPipeline: pinned host buffers, per-step H2D + D2H on a copy stream overlapped with the previous/next step's compute"},
+                       "e2e": "HostPipeline: pinned host buffers, per-step H2D and D2H on two copy streams overlapped with the previous/next step's compute"},
             "realtime_x": value / REALTIME_FRAMES_PER_S,
             "whole_path_tensor_frac": value / world * FLOP_PER_FRAME / (peak * 1e12),
+            "whole_path_tensor_frac_burst": value / world * FLOP_PER_FRAME / (burst * 1e12),
             "latency_p50_ms_b1_t128": lat_p50,
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches_per_step * K),
             "clocks": clocks,
-            "phase_ms": {k: round(v, 4) for k, v in phase_ms.items()},
+            "phase_ms": phase_ms,
             "roofline": {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": f"{peak_src} bf16_tflops_sustained",
+                         "frac": achieved / peak, "frac_of_burst_peak": achieved / burst, "traffic": traffic,
+                         "peak_source": f"{peak_src} bf16_tflops_sustained ({peak}); burst {burst}",
                          "algorithmic_flop_per_launch_group": dom_flops},
             "wall_s_timed_region": wall,
         }
+        if configs:
+            line["configs"] = configs
+        if world == 1 and not args.no_configs:
+            line["gpu_eager_baseline"] = gpu_eager_baseline(dev, B, T, x, c_org, c_trg)
         if not args.no_cpu_baseline and world == 1:     # the CPU leg is an N=1 measurement (rank 0 would share the host with the other ranks)
-            fps, ms, cores = time_oracle(args.cpu_sample_batch, T, 3, 1)
-            line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                                    "sample": f"{args.cpu_sample_batch} of the {B} utterances x {T} frames, 3 timed passes of the oracle port (torch CPU fp32)"}
+            r = time_cpu_reference(B, T, 3, 1, budget_s=40.0)
+            line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()

@@ -107,6 +107,11 @@ int avc_forward_bn_train(avc_handle h, const float* x, const float* c_org, const
 /* Number of kernel launches the last avc_forward/avc_encode enqueued (for bench.py's gpu_launches). */
 int64_t avc_last_launch_count(avc_handle h);
 
+/* Number of plan sets (tensor maps + launch geometry of one (workspace, B, T, mode)) built since avc_create.  The
+ * context keeps the 8 most recently used sets, so alternating shapes - length buckets of a conversion job, a B=1 call
+ * between B=256 steps, the training pair's encode-only pass - do not rebuild them (tests, diagnostics). */
+int64_t avc_plan_builds(avc_handle h);
+
 /* Optional per-phase device timing of the NEXT runs: CUDA events are recorded on the caller's stream at phase
  * boundaries; avc_get_profile() synchronises on the last one and returns the milliseconds spent per phase in the
  * most recent run (ms must have room for AVC_PHASE_COUNT floats).  bench.py uses this for the roofline object. */
@@ -240,7 +245,7 @@ void avc_voc_destroy(avc_voc_handle h);
 const char* avc_last_error(avc_handle h);
 
 /* ABI version; bumped on any signature change. */
-int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder; 5: avc_forward_bn_train */
+int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder; 5: avc_forward_bn_train; 6: avc_plan_builds (plan LRU) */
 
 #ifdef __cplusplus
 }

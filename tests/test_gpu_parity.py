@@ -192,3 +192,131 @@ def test_batches_beyond_one_recurrence_launch(B, T):
     ref_mel, ref_post, ref_codes = O.generator_forward(synth_state_dict(0), x[idx], c_org[idx], c_trg[idx])
     assert float((post_s.cpu() - ref_post).abs().max()) <= BF16_POST_TOL
     assert torch.isfinite(post).all()
+
+
+# ---- full-size parity (BASELINE.json configs 2, 3, 5) against the oracle on sampled rows ----------------------------
+def _check_rows(precision, got, ref, rows_note):
+    mel, post, codes = got
+    r_mel, r_post, r_codes = ref
+    tol = FP32_TOL if precision == "fp32" else BF16_POST_TOL
+    e_mel, e_post = float((mel.cpu() - r_mel).abs().max()), float((post.cpu() - r_post).abs().max())
+    cos = float(torch.nn.functional.cosine_similarity(codes.cpu(), r_codes, dim=1).min())
+    print(f"{rows_note}[{precision}]: mel {e_mel:.2e} post {e_post:.2e} cos {cos:.6f}")
+    assert e_mel <= tol and e_post <= tol and cos >= BF16_COS
+    if precision == "fp32":
+        assert float((codes.cpu() - r_codes).abs().max()) <= FP32_TOL
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_config2_sixteen_rows_match_oracle(precision):
+    """Config 2 (B=256, T=128): 16 seeded-random rows of the full batch against the oracle (rows are independent, so the
+    oracle runs on those rows alone)."""
+    from oracle import autovc_oracle as O
+    m = model(precision)
+    x, c_org, c_trg = synth_inputs(256, 128, seed=1234)
+    mel, post, codes = m(x.cuda(), c_org.cuda(), c_trg.cuda())
+    idx = torch.from_numpy(np.sort(np.random.default_rng(7).choice(256, size=16, replace=False)))
+    ref = O.generator_forward(synth_state_dict(0), x[idx], c_org[idx], c_trg[idx])
+    _check_rows(precision, (mel[idx.cuda()], post[idx.cuda()], codes[idx.cuda()]), ref, "config2 rows " + str(idx.tolist()))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_config3_full_batch_rows_match_oracle(precision):
+    """Config 3 at its full size (B=64, T=1024: the 32-utterance lstm2 tiles, 2048 dependent lstm2 steps): rows at both
+    ends of both tiles against the oracle."""
+    from oracle import autovc_oracle as O
+    m = model(precision)
+    x, c_org, c_trg = synth_inputs(64, 1024, seed=33)
+    mel, post, codes = m(x.cuda(), c_org.cuda(), c_trg.cuda())
+    idx = torch.tensor([0, 31, 32, 63])
+    ref = O.generator_forward(synth_state_dict(0), x[idx], c_org[idx], c_trg[idx])
+    _check_rows(precision, (mel[idx.cuda()], post[idx.cuda()], codes[idx.cuda()]), ref, "config3 rows 0/31/32/63")
+
+
+def test_config5_bf16_pair_full_batch_rows_match_oracle():
+    """Config 5's per-GPU share (B=256, T=128, eval-mode BatchNorm), bf16: pass 1 forward(X,c,c) and pass 2
+    forward(mel_post,c,None) on four sampled rows against the oracle's pair on those rows."""
+    from oracle import autovc_oracle as O
+    m = model("bf16")
+    x, c_org, _ = synth_inputs(256, 128, seed=58)
+    mel, post, codes = m(x.cuda(), c_org.cuda(), c_org.cuda())
+    codes2 = m(post, c_org.cuda(), None)
+    idx = torch.tensor([0, 100, 200, 255])
+    sd = synth_state_dict(0)
+    r_mel, r_post, r_codes = O.generator_forward(sd, x[idx], c_org[idx], c_org[idx])
+    r_codes2 = O.generator_forward(sd, r_post, c_org[idx], None)
+    _check_rows("bf16", (mel[idx.cuda()], post[idx.cuda()], codes[idx.cuda()]), (r_mel, r_post, r_codes), "config5 pass 1")
+    cos2 = float(torch.nn.functional.cosine_similarity(codes2[idx.cuda()].cpu(), r_codes2, dim=1).min())
+    print(f"config5 pass 2: cos(codes) {cos2:.6f}")
+    assert cos2 >= BF16_COS
+
+
+def test_recurrence_exchange_is_bitwise_reproducible_under_stress():
+    """The in-band h exchange (ll_lstm.cu: the data is the flag) claims a timing-independent accumulation order: 200
+    forwards of config 3 (B=64, T=1024: 0.8 M exchanged step tiles in all) must give bitwise-identical outputs."""
+    m = model("bf16")
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(64, 1024, seed=91))
+    first = [t.clone() for t in m(x, c_org, c_trg)]
+    out = tuple(torch.empty_like(t) for t in first)
+    bad = 0
+    for _ in range(200):
+        m(x, c_org, c_trg, out=out)
+        bad += int(not all(torch.equal(a, b) for a, b in zip(out, first)))
+    assert bad == 0, f"{bad} of 200 runs differed"
+    assert torch.isfinite(first[1]).all()
+
+
+def test_plan_cache_keeps_alternating_shapes():
+    """Alternating shapes and modes (length buckets, B=1 after a big batch, the encode-only pass) must not rebuild tensor
+    maps: each (B, T, mode) is built once and results stay identical."""
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cuda", verbose=False, precision="bf16")
+    m.load_state_dict(synth_state_dict(0))
+    big = tuple(t.cuda() for t in synth_inputs(64, 128, seed=5))      # sizes the workspace first: its address then stays put
+    small = tuple(t.cuda() for t in synth_inputs(1, 128, seed=6))
+    rag = tuple(t.cuda() for t in synth_inputs(3, 100, seed=7))
+    want = [m(*big), m(*small), m(*rag), m(big[0], big[1], None)]
+    eng = m._engine(torch.device("cuda", 0))
+    builds = eng.plan_builds
+    for _ in range(3):
+        got = [m(*big), m(*small), m(*rag), m(big[0], big[1], None)]
+        for g, w in zip(got, want):
+            for a, b in zip(g if isinstance(g, tuple) else (g,), w if isinstance(w, tuple) else (w,)):
+                assert torch.equal(a, b)
+    assert eng.plan_builds == builds, (eng.plan_builds, builds)
+
+
+def test_weight_changes_reach_the_packed_copy():
+    """In-place updates through autograd-visible ops are picked up automatically; writes through `.data` (the reference's
+    own load_flattened_params, model.py:385-392) need invalidate() - and this class's load_flattened_params does it."""
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cuda", verbose=False, precision="fp32")
+    m.load_state_dict(synth_state_dict(0))
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(2, 64, seed=2))
+    base = m(x, c_org, c_trg)[1].clone()
+    w = m.decoder.linear_projection.linear_layer.bias
+    with torch.no_grad():
+        w.add_(0.5)
+    shifted = m(x, c_org, c_trg)[1]
+    assert float((shifted - base).abs().max()) > 0.1
+    w.data.sub_(0.5)                        # invisible to the version counter ...
+    assert torch.equal(m(x, c_org, c_trg)[1], shifted)
+    m.invalidate()                          # ... until the caller says so
+    assert float((m(x, c_org, c_trg)[1] - base).abs().max()) <= 1e-6
+    flat = m.flatten_params()
+    m.load_flattened_params(flat * 0 + flat)
+    assert float((m(x, c_org, c_trg)[1] - base).abs().max()) <= 1e-6
+
+
+def test_caller_device_is_restored():
+    """avc_forward switches to the context's device for its launches and must leave the caller's current device alone."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cuda:1", verbose=False, precision="bf16")
+    m.load_state_dict(synth_state_dict(0))
+    x, c_org, c_trg = (t.to("cuda:1") for t in synth_inputs(2, 64, seed=2))
+    torch.cuda.set_device(0)
+    m(x, c_org, c_trg)
+    probe = torch.empty(1, device="cuda")        # allocated on the CUDA runtime's current device
+    assert torch.cuda.current_device() == 0 and probe.device.index == 0

@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     lib = ctypes.CDLL(built_lib)
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/autovc_b200.h but not exported"
-    assert lib.avc_abi_version() == 5
+    assert lib.avc_abi_version() == 6
 
 
 def test_state_dict_contract():
@@ -156,3 +156,54 @@ def test_vocoder_state_dict_contract_and_host_packing(built_lib):
     assert fold_params(35200, 11000, 550) == (3, 0) and fold_params(6050, 2950, 50) == (2, 0) and fold_params(6600, 1500, 100) == (5, 1600)
     with pytest.raises(RuntimeError):
         WaveRNN(device="cpu").condition(torch.zeros(1, 80, 30))
+
+
+def test_weight_tracking_key_follows_in_place_updates_and_invalidate():
+    """PackedWeightsMixin: the key the modules compare before re-packing their weights (no GPU needed)."""
+    import torch
+    import autovc_b200
+    m = autovc_b200.AutoEncoder(device="cpu", verbose=False)
+    k0 = m._weights_key()
+    p = next(m.parameters())
+    p.data.mul_(1.0)                                   # a write through .data is invisible to Tensor._version ...
+    assert m._weights_key() == k0
+    m.invalidate()                                     # ... the documented hook covers it
+    k1 = m._weights_key()
+    assert k1 != k0
+    with torch.no_grad():
+        p.mul_(1.0)
+    k2 = m._weights_key()
+    assert k2 != k1
+    m.encoder.convolutions[0][1].running_mean.add_(0.0)
+    k3 = m._weights_key()
+    assert k3[0] != k2[0] and k3[1] == k2[1]           # running statistics only touch the first key
+    flat = m.flatten_params()
+    assert flat.numel() == sum(q.numel() for q in m.parameters())
+    m.load_flattened_params(flat.clone())
+    assert m._weights_key() != k3
+    m.load_state_dict(m.state_dict())
+    assert m._weights_key()[0][0] > k3[0][0]
+    for cls in (autovc_b200.SpeakerEncoder, autovc_b200.WaveRNN):
+        mod = cls(device="cpu") if cls is autovc_b200.WaveRNN else cls(device="cpu", verbose=False)
+        a = mod._weights_key()
+        mod.invalidate()
+        assert mod._weights_key() != a
+
+
+def test_staged_reference_matches_its_manifest():
+    """oracle/_ref (staged by oracle/make_ref.py in the build container) is the unmodified reference: every file's
+    SHA-256 still equals the one recorded at copy time, and - where /root/reference is present - the source's."""
+    import hashlib
+    import json
+    import os
+    import pytest
+    from oracle import ref_loader
+    if not os.path.isdir(os.path.join(ref_loader.STAGED, "autovc")):
+        pytest.skip("oracle/_ref not staged (run python oracle/make_ref.py in the build container)")
+    assert ref_loader.verify()
+    files = json.load(open(os.path.join(ref_loader.STAGED, "MANIFEST.json")))["files"]
+    assert "autovc/auto_encoder/model.py" in files
+    if os.path.isdir(ref_loader.LIVE):
+        for rel, sha in files.items():
+            with open(os.path.join(ref_loader.LIVE, rel), "rb") as f:
+                assert hashlib.sha256(f.read()).hexdigest() == sha, rel
