@@ -139,6 +139,12 @@ int fail(avc_ctx* h, int code, const char* fmt, ...) {
     return code;
 }
 
+// unidirectional LSTM layers of this hidden size run on the tensor-core recurrence (ll_lstm.cu): decides the kernel at run
+// time AND the gate-row prescale at pack time, so both must read the same predicate
+bool ll_eligible(const avc_ctx* h, int H) {
+    return h->precision == AVC_PREC_BF16 && !h->force_simt && !h->simt_lstm && H % 256 == 0 && H <= 1024;
+}
+
 int act_type(const avc_ctx* h) { return h->precision == AVC_PREC_FP32 ? DT_F32 : DT_BF16; }
 int post_type(const avc_ctx* h) { return h->precision == AVC_PREC_FP32 ? DT_F32 : DT_F16; }
 
@@ -187,7 +193,10 @@ bool pack_conv(avc_ctx* h, Layer& L, const std::string& prefix, int cin, int cou
 
 // nn.LSTM matrices -> unit-major gate rows: packed row d*4H + u*4 + g  <-  PyTorch row g*H + u of direction d.
 // ih: [ndir*4H][K] with bias = b_ih + b_hh;  hh: [ndir*4H][H], no bias.
-bool pack_lstm(avc_ctx* h, Layer& Lih, Layer& Lhh, const std::string& prefix, int layer, int in_k, int H, bool bidir) {
+// `prescale` (layers that run on the tensor-core recurrence, ll_lstm.cu): the rows of the sigmoid gates (i, f, o) of W_ih, W_hh
+// and the bias are multiplied by 0.5 - exact in every binary format - so that the kernel's gate pre-activation already is the
+// argument of  sigmoid(x) = 0.5 tanh(0.5 x) + 0.5  and the epilogue saves one multiply per gate value.
+bool pack_lstm(avc_ctx* h, Layer& Lih, Layer& Lhh, const std::string& prefix, int layer, int in_k, int H, bool bidir, bool prescale = false) {
     const int ndir = bidir ? 2 : 1;
     Lih.taps = 1; Lih.N = ndir * 4 * H; Lih.K = in_k; Lih.Kp = round_up(in_k, 16); Lih.Cin = in_k; Lih.Cp = Lih.Kp;
     Lhh.taps = 1; Lhh.N = ndir * 4 * H; Lhh.K = H; Lhh.Kp = H; Lhh.Cin = H; Lhh.Cp = H;
@@ -206,6 +215,11 @@ bool pack_lstm(avc_ctx* h, Layer& Lih, Layer& Lhh, const std::string& prefix, in
                 memcpy(&Lih.w[(size_t)dst * Lih.Kp], &(*wih)[(size_t)src * in_k], sizeof(float) * in_k);
                 memcpy(&Lhh.w[(size_t)dst * Lhh.Kp], &(*whh)[(size_t)src * H], sizeof(float) * H);
                 Lih.b[dst] = (*bih)[src] + (*bhh)[src];
+                if (prescale && g != 2) {
+                    for (int k = 0; k < in_k; ++k) Lih.w[(size_t)dst * Lih.Kp + k] *= 0.5f;
+                    for (int k = 0; k < H; ++k) Lhh.w[(size_t)dst * Lhh.Kp + k] *= 0.5f;
+                    Lih.b[dst] *= 0.5f;
+                }
             }
     }
     return true;
@@ -378,7 +392,7 @@ struct Runner {
     //   Gx: [B][Tg][ndir*4H] fp32 (row for frame t is t/gx_div);  Y: [B][T][ndir*H] of h_type.
     // true when lstm() takes the in-band-exchange tensor-core kernel for this layer (which also accepts fp16 Gx)
     bool ll_path(int lid_hh, int h_type, int H, int ndir) const {
-        return use_tc() && !h->simt_lstm && ndir == 1 && h_type == DT_BF16 && h->layers[lid_hh].w_type == DT_BF16 && H % 256 == 0 && H <= 1024;
+        return ll_eligible(h, H) && ndir == 1 && h_type == DT_BF16 && h->layers[lid_hh].w_type == DT_BF16;
     }
     // fp16 gate pre-activations for the big recurrent layers: halves the Gx write + read (1 GB per forward at config 2)
     int gx_type(int lid_hh, int h_type, int H) const { return ll_path(lid_hh, h_type, H, 1) && !h->gx_f32 ? DT_F16 : DT_F32; }
@@ -668,12 +682,12 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
     ok = ok && pack_conv(h, L[L_ENC_CONV2], "encoder.convolutions.2", CONV_CH, CONV_CH);
     ok = ok && pack_lstm(h, L[L_ENC_L0_IH], L[L_ENC_L0_HH], "encoder.lstm", 0, CONV_CH, dn, true);
     ok = ok && pack_lstm(h, L[L_ENC_L1_IH], L[L_ENC_L1_HH], "encoder.lstm", 1, 2 * dn, dn, true);
-    ok = ok && pack_lstm(h, L[L_DEC_LSTM1_IH], L[L_DEC_LSTM1_HH], "decoder.lstm1", 0, 2 * dn + E, P, false);
+    ok = ok && pack_lstm(h, L[L_DEC_LSTM1_IH], L[L_DEC_LSTM1_HH], "decoder.lstm1", 0, 2 * dn + E, P, false, ll_eligible(h, P));
     ok = ok && pack_conv(h, L[L_DEC_CONV0], "decoder.convolutions.0", P, P);
     ok = ok && pack_conv(h, L[L_DEC_CONV1], "decoder.convolutions.1", P, P);
     ok = ok && pack_conv(h, L[L_DEC_CONV2], "decoder.convolutions.2", P, P);
-    ok = ok && pack_lstm(h, L[L_DEC_L2_0_IH], L[L_DEC_L2_0_HH], "decoder.lstm2", 0, P, LSTM2_H, false);
-    ok = ok && pack_lstm(h, L[L_DEC_L2_1_IH], L[L_DEC_L2_1_HH], "decoder.lstm2", 1, LSTM2_H, LSTM2_H, false);
+    ok = ok && pack_lstm(h, L[L_DEC_L2_0_IH], L[L_DEC_L2_0_HH], "decoder.lstm2", 0, P, LSTM2_H, false, ll_eligible(h, LSTM2_H));
+    ok = ok && pack_lstm(h, L[L_DEC_L2_1_IH], L[L_DEC_L2_1_HH], "decoder.lstm2", 1, LSTM2_H, LSTM2_H, false, ll_eligible(h, LSTM2_H));
     ok = ok && pack_linear(h, L[L_DEC_LINEAR], "decoder.linear_projection.linear_layer", LSTM2_H, N_MELS);
     ok = ok && pack_conv(h, L[L_POST_CONV0], "postnet.convolutions.0", N_MELS, CONV_CH);
     ok = ok && pack_conv(h, L[L_POST_CONV1], "postnet.convolutions.1", CONV_CH, CONV_CH);
@@ -825,7 +839,7 @@ int avc_se_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
     Layer* L = h->layers;
     bool ok = true;
     for (int l = 0; l < SE_LAYERS; ++l)
-        ok = ok && pack_lstm(h, L[L_SE_L0_IH + 2 * l], L[L_SE_L0_HH + 2 * l], "lstm", l, l == 0 ? SE_MELS : SE_H, SE_H, false);
+        ok = ok && pack_lstm(h, L[L_SE_L0_IH + 2 * l], L[L_SE_L0_HH + 2 * l], "lstm", l, l == 0 ? SE_MELS : SE_H, SE_H, false, ll_eligible(h, SE_H));
     ok = ok && pack_linear(h, L[L_SE_LINEAR], "linear", SE_H, SE_EMB);
     h->raw.clear();
     if (!ok) return AVC_ERR_MISSING_WEIGHT;

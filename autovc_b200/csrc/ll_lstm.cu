@@ -91,7 +91,8 @@ struct LlLstmArgs {
     long long* trace;            // optional clock64 trace of CTA (0,0) (AVC_LSTM_TRACE=1), nullptr normally
 };
 
-constexpr int TRACE_T0 = 8, TRACE_STEPS = 8, TRACE_PTS = 32;   // 0..5 phase stamps, 8+kc: chunk kc seen by the MMA thread
+constexpr int TRACE_T0 = 8, TRACE_STEPS = 8, TRACE_PTS = 32;
+constexpr int TRACE_WORDS = (2 * TRACE_STEPS + 1) * TRACE_PTS;   // 0..5 phase stamps, 8+kc: chunk kc seen by the MMA thread
 #define AVC_TRACE(pt) do { if (a.trace && blockIdx.x == 0 && blockIdx.y == 0 && t >= TRACE_T0 && t < TRACE_T0 + TRACE_STEPS) \
     a.trace[(t - TRACE_T0) * TRACE_PTS + (pt)] = clock64(); } while (0)
 
@@ -127,6 +128,9 @@ __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// c' = f c + i g with ONE fixed rounding order in every kernel of this file (rows of a batch must not depend on which kernel
+// variant the batch size selects): the product i g is rounded, then fused into f c
+__device__ __forceinline__ float cell_update(float fg, float c, float ig, float gg) { return fmaf(fg, c, __fmul_rn(ig, gg)); }
 __device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
 template <int NKB, bool GXH, int TN>
@@ -234,6 +238,8 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         const int gj = lane & 3;                              // gate of this lane: 0=i 1=f 2=g 3=o
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * CPT);
         const float act_s = gj == 2 ? 2.0f : 1.0f, act_o = gj == 2 ? -1.0f : 0.0f;   // tanh(x) = 2 sigmoid(2x) - 1
+        // the sigmoid gates' rows of W_ih, W_hh and the bias are packed pre-multiplied by 0.5 (api.cu::pack_lstm): the
+        // pre-activation x' is 0.5 x for i, f, o and x for g, i.e. always the argument of the tanh below
         float c[CPT / 4];
 #pragma unroll
         for (int k = 0; k < CPT / 4; ++k) c[k] = 0.0f;
@@ -409,14 +415,14 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 for (int k = 0; k < CPT; ++k) {
                     const float x = act[k] + gx_at(k);
                     float th;
-                    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(ps * x));
+                    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(x));
                     act[k] = fmaf(ps, th, po);
                 }
             } else {
 #pragma unroll
                 for (int k = 0; k < CPT; ++k) {
                     const float x = act[k] + gx_at(k);
-                    act[k] = __fdividef(act_s, 1.0f + __expf(-act_s * x)) + act_o;
+                    act[k] = __fdividef(act_s, 1.0f + __expf(-2.0f * x)) + act_o;
                 }
             }
             if (threadIdx.x == 0) AVC_TRACE(6);
@@ -444,7 +450,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     const float e1 = (gj & 1) ? kx : rx, e3 = (gj & 1) ? ky : ry;     // gates (gj & 2) + 1 and its ^ 2
                     const float ig = (gj & 2) ? e2 : e0, gg = (gj & 2) ? e0 : e2;
                     const float fg = (gj & 2) ? e3 : e1, og = (gj & 2) ? e1 : e3;
-                    c[kk] = fg * c[kk] + ig * gg;
+                    c[kk] = cell_update(fg, c[kk], ig, gg);
                     float tc;
                     if (a.approx) asm("tanh.approx.f32 %0, %1;" : "=f"(tc) : "f"(c[kk]));
                     else tc = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * c[kk]));
@@ -487,6 +493,385 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     }
 }
 
+// =====================================================================================================================
+// Pipelined variant: TWO independent 32-utterance sub-tiles per CTA pair.
+//
+// A step of one tile is a dependent chain  exchange (store -> visible -> load wave) -> MMAs -> gate epilogue  in which every
+// unit idles while the others work.  Two sub-tiles of one CTA pair are independent chains over the same resident W_hh: while
+// sub-tile A's h crosses L2, sub-tile B's MMAs and epilogue run.  Roles (17 warps, 96 registers per thread):
+//   warps 0-7    sub-tile 0: loaders of its h_{t-1} rows (16 rows per CTA x H) AND its gate epilogue (16 columns per thread)
+//   warps 8-15   sub-tile 1: the same
+//   warps 16,17  MMA issuers (leader CTA), one K half each into its own accumulator (the one-tile kernel's split, so a row's
+//                result is bitwise the same whichever kernel its batch size selects), each strictly alternating
+//                A(t), B(t), A(t+1), ... in program order.  That order (a) keeps the accumulation order independent of
+//                timing and (b) pins the two chains one MMA phase apart: two free-running chains fall into lockstep and then
+//                share every unit at half rate, which is the one-tile kernel again (profiles/r1_ll_lstm_step_timeline.md).
+//                One warp issues an N = 32 MMA every ~27 cycles (descriptor set-up), the pipe retires one every ~17: two.
+// Two accumulators per sub-tile (128 columns in all) leave room for 12 of the 16 K chunks of W_hh in tensor memory.
+// The 16 group warps never meet at a CTA-level barrier inside the time loop: a warp waits for its own h pieces, for the
+// accumulator mbarrier and for nothing else.  (Profile of the barrier version, profiles/r2_ll2_lstm_notes.md: 15 % of all warp
+// samples sat at the group barrier in front of the epilogue, i.e. behind the group's slowest poller, and another 5 % at the one in
+// front of the stores.)  Hence: the Gx_t block is staged warp-privately (a warp copies what its own lanes read), the 4x4 gate
+// transpose goes through a per-warp shared-memory tile (16 STS + 4 LDS.128 instead of 16 shuffles + ~60 selects), h_t leaves
+// straight from registers as 32-bit words (one lane-pair exchange), and the sigmoid rows arrive pre-scaled
+// (api.cu::pack_lstm).  Exchange protocol and operand layout are the one-tile kernel's.  No acc_empty barrier: a
+// sub-tile's operands for step t+1 are published by the very warps that read its accumulators of step t (after their named
+// barrier), so "operands complete" implies "accumulators drained" in both CTAs.
+// =====================================================================================================================
+namespace p2 {
+constexpr int SUB_N = 32;                            // utterances per sub-tile = UMMA N
+constexpr int SUB_ROWS = SUB_N / 2;                  // rows of h staged per CTA and sub-tile
+constexpr int GROUP_WARPS = 8, GROUP_THREADS = GROUP_WARPS * 32;
+constexpr int ISSUE_WARP = 2 * GROUP_WARPS;          // 16, 17: one K half each
+constexpr int THREADS = (2 * GROUP_WARPS + 2) * 32;  // 576
+constexpr uint32_t D_COLS2 = 4 * SUB_N;              // two accumulators (K halves) per sub-tile: columns (2 g + ih) * 32
+constexpr int MAX_TMEM_CHUNKS2 = (512 - (int)D_COLS2) / 32;    // 12
+constexpr int GT_BYTES = GROUP_WARPS * 16 * 32 * 4;  // 16 KiB per sub-tile: per warp a [16 columns][32 gate rows] fp32 transpose tile
+constexpr int HBLK2 = SUB_ROWS * KBLK * 2;           // 2 KiB per CTA, sub-tile and chunk
+__host__ __device__ constexpr int gx2_bytes(bool gxh) { return SUB_N * MROWS * (gxh ? 2 : 4); }   // one Gx_t block of a sub-tile: 8 KiB (fp16) / 16 KiB (fp32)
+constexpr int CPT2 = SUB_N / 2;                      // accumulator columns per epilogue thread
+constexpr int TR_PTS = 32;                           // trace points per (step, sub-tile)
+}  // namespace p2
+
+#define AVC_TRACE2(g, pt) do { if (a.trace && blockIdx.x == 0 && blockIdx.y == 0 && t >= TRACE_T0 && t < TRACE_T0 + TRACE_STEPS) \
+    a.trace[((t - TRACE_T0) * 2 + (g)) * p2::TR_PTS + (pt)] = clock64(); } while (0)
+
+template <int NKB, bool GXH>
+__global__ void __launch_bounds__(p2::THREADS, 1)
+ll2_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
+    using namespace p2;
+    constexpr int NKB_T = NKB < MAX_TMEM_CHUNKS2 ? NKB : MAX_TMEM_CHUNKS2;
+    constexpr int NKB_S = NKB - NKB_T;
+    constexpr int PSTRIDE = SUB_N * PLANE_ELEMS;          // elements between planes of a 32-row tile of Yx
+    static_assert(NKB == 16 || NKB == 8 || NKB == 4, "H must be 1024, 512 or 256");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sW = smem;                                        // NKB_S x 16 KiB
+    uint8_t* sH = sW + NKB_S * W_BLK_BYTES;                    // [2 sub-tiles][NKB][2 KiB]
+    constexpr int GXB = gx2_bytes(GXH);
+    uint8_t* sGx = sH + 2 * NKB * HBLK2;                       // [2 sub-tiles][2 buffers][GXB]: Gx_t is staged ONE STEP AHEAD
+    uint8_t* sGT = sGx + 4 * GXB;                              // [2][16 KiB]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sGT + 2 * GT_BYTES);
+    uint64_t* wfull = bars;                                    // [1]
+    uint64_t* acc_full = bars + 1;                             // [2] the MMAs (both K halves) of a sub-tile's step are complete
+    uint64_t* gfull = bars + 4;                                // [2][4] chunk quarter q of sub-tile g is in shared memory (both CTAs)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const int ns = blockIdx.x;            // unit slice (32 units)
+    const int bt = blockIdx.y;            // pair of 32-utterance sub-tiles
+    const uint32_t crank = ptx::cluster_ctarank();
+    const size_t tile_elems = (size_t)a.H * SUB_N;                      // one (t, 32-row tile) block of Yx
+    const size_t step_elems = tile_elems * a.tiles;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            if (NKB_S > 0) ptx::prefetch_tmap(&tmW);
+            ptx::mbar_init(wfull, 1);
+            for (int i = 0; i < 8; ++i) ptx::mbar_init(&gfull[i], 2 * (GROUP_WARPS / 4));   // 2 loader warps per quarter in each CTA
+            ptx::mbar_init(&acc_full[0], 2);                                                 // one commit per issuing warp
+            ptx::mbar_init(&acc_full[1], 2);
+            ptx::fence_barrier_init();
+        }
+        __syncwarp();
+        ptx::tmem_alloc_pair<TMEM_COLS>(tmem_slot);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();
+    ptx::tc_fence_after();
+    if (*tmem_slot != 0u) { if (threadIdx.x == 0) printf("autovc_b200: unexpected TMEM base %u\n", *tmem_slot); __trap(); }
+    constexpr uint32_t tmem_base = 0u;
+    constexpr uint32_t W_COL = D_COLS2;
+
+    // ---- resident W: chunks 0..NKB_T-1 -> tensor memory, the rest -> shared memory ----
+    if (warp < 4) {
+        const int R = warp * 32 + lane;
+        const __nv_bfloat16* wrow = a.Whh + (size_t)(ns * MROWS + R) * a.H;
+        const uint32_t wl = tmem_base + W_COL + ((uint32_t)(warp * 32) << 16);
+        for (int kc = 0; kc < NKB_T; ++kc) {
+            uint4 v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __ldg(reinterpret_cast<const uint4*>(wrow + kc * KBLK) + i);
+            ptx::tmem_st32(wl + (uint32_t)(kc * 32), reinterpret_cast<const uint32_t(&)[32]>(v));
+        }
+        ptx::tmem_st_wait();
+    }
+    if (NKB_S > 0 && warp == 4 && lane == 0) {
+        ptx::mbar_expect_tx(wfull, (uint32_t)(NKB_S * W_BLK_BYTES));
+        for (int i = 0; i < NKB_S; ++i)
+            ptx::tma_load_2d(sW + i * W_BLK_BYTES, &tmW, wfull, (NKB_T + i) * KBLK, ns * MROWS);
+        ptx::mbar_wait(wfull, 0);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();
+    ptx::tc_fence_after();
+
+    if (warp >= ISSUE_WARP) {
+        // ===================== MMA issuers (leader CTA): K half ih of A(t), B(t), A(t+1), ... =====================
+        if (crank == 0) {
+            const uint32_t sH_u = ptx::smem_u32(sH), sW_u = ptx::smem_u32(sW);
+            auto run = [&](auto IH) {
+                constexpr int ih = decltype(IH)::value;
+                for (int t = 1; t < a.T; ++t) {
+                    const uint32_t par = (uint32_t)(t - 1) & 1;
+                    auto issue_sub = [&](auto G) {
+                        constexpr int g = decltype(G)::value;
+                        constexpr uint32_t d_tmem = tmem_base + (uint32_t)((2 * g + ih) * SUB_N);
+                        // Issue loop shape: ROLLED over the K chunks with running descriptor words.  ptxas then keeps the whole
+                        // sequence on the uniform datapath (UIADD3 / UMOV between the UTCHMMAs); unrolled, it computes every
+                        // descriptor in vector registers and pays ~2 R2UR per MMA - 27 cycles per MMA from one warp, against
+                        // the 17 the pipe needs at N = 32 (tools/micro/mma_burst.cu, profiles/r2_ll2_lstm_notes.md).
+                        auto issue_quarter = [&](auto Q) {
+                            constexpr int q = decltype(Q)::value;
+                            constexpr int c0 = q * (NKB / 4), c1 = c0 + NKB / 4;
+                            constexpr int ts_end = c1 <= NKB_T ? c1 : (c0 < NKB_T ? NKB_T : c0);   // [c0, ts_end) A in TMEM, [ts_end, c1) A in smem
+                            ptx::mbar_wait(&gfull[g * 4 + q], par);
+                            ptx::tc_fence_after();
+                            if (q == 0 && ih == 0 && lane == 0) AVC_TRACE2(g, 8);
+                            if (lane == 0) AVC_TRACE2(g, 10 + q);
+                            const uint64_t bd0 = ptx::umma_desc_sw128(sH_u + (uint32_t)((g * NKB + c0) * HBLK2));
+                            const uint32_t b_hi = (uint32_t)(bd0 >> 32);
+                            uint32_t b_lo = (uint32_t)bd0;
+                            uint32_t a_t = tmem_base + W_COL + (uint32_t)(c0 * 32);
+#pragma unroll 1
+                            for (int c = c0; c < ts_end; ++c) {
+#pragma unroll
+                                for (int k = 0; k < KBLK / 16; ++k) {
+                                    ptx::umma2_f16_ts_warp(d_tmem, a_t, ((uint64_t)b_hi << 32) | b_lo, a.idesc, (c != ih * (NKB / 2) || k != 0) ? 1u : 0u);
+                                    a_t += 8; b_lo += 2;
+                                }
+                                b_lo += (uint32_t)(HBLK2 >> 4) - 2 * (KBLK / 16);
+                            }
+                            if constexpr (ts_end < c1) {
+                                const uint64_t ad0 = ptx::umma_desc_sw128(sW_u + (uint32_t)((ts_end - NKB_T) * W_BLK_BYTES));
+                                const uint32_t a_hi = (uint32_t)(ad0 >> 32);
+                                uint32_t a_lo = (uint32_t)ad0;
+#pragma unroll 1
+                                for (int c = ts_end; c < c1; ++c) {
+#pragma unroll
+                                    for (int k = 0; k < KBLK / 16; ++k) {
+                                        ptx::umma2_f16_warp(d_tmem, ((uint64_t)a_hi << 32) | a_lo, ((uint64_t)b_hi << 32) | b_lo, a.idesc,
+                                                            (c != ih * (NKB / 2) || k != 0) ? 1u : 0u);
+                                        a_lo += 2; b_lo += 2;
+                                    }
+                                    a_lo += (uint32_t)(W_BLK_BYTES >> 4) - 2 * (KBLK / 16);
+                                    b_lo += (uint32_t)(HBLK2 >> 4) - 2 * (KBLK / 16);
+                                }
+                            }
+                        };
+                        issue_quarter(std::integral_constant<int, 2 * ih>{});
+                        issue_quarter(std::integral_constant<int, 2 * ih + 1>{});
+                        ptx::umma2_commit_warp(&acc_full[g]);       // -> acc_full[g] of BOTH CTAs
+                        if (ih == 1 && lane == 0) AVC_TRACE2(g, 9);
+                    };
+                    issue_sub(std::integral_constant<int, 0>{});
+                    issue_sub(std::integral_constant<int, 1>{});
+                }
+            };
+            if (warp == ISSUE_WARP) run(std::integral_constant<int, 0>{}); else run(std::integral_constant<int, 1>{});
+        }
+    } else {
+        // ===================== sub-tile group g: loaders + epilogue =====================
+        const int g = warp >> 3, wg = warp & 7;
+        const int tg = (int)(threadIdx.x & (GROUP_THREADS - 1));
+        const int b0 = bt * (2 * SUB_N) + g * SUB_N;
+        __nv_bfloat16* yx_tile = a.Yx + (size_t)(a.tile0 + bt * 2 + g) * tile_elems;    // + t * step_elems
+        uint64_t* my_acc = &acc_full[g];
+        // ---- loader geometry: warp wg owns chunks 2wg, 2wg+1; piece i: chunk 2wg + (i>>2), plane 2(i&3) + (lane>>4), row lane&15 ----
+        const int lrow = lane & 15, lpl = lane >> 4;
+        const uint32_t sH_g = ptx::smem_u32(sH) + (uint32_t)(g * NKB * HBLK2);
+        constexpr int CPW = NKB / GROUP_WARPS > 0 ? NKB / GROUP_WARPS : 1;      // chunks per warp: 2 (H=1024), 1 (H=512)
+        constexpr int WPC2 = NKB >= GROUP_WARPS ? 1 : GROUP_WARPS / NKB;          // warps per chunk: 1, or 2 (H=256)
+        constexpr int NP = SUB_ROWS * 8 * NKB / GROUP_THREADS;                  // 16-byte pieces per lane and step: 8 / 4 / 2
+        auto piece_chunk = [&](int i) { return WPC2 == 1 ? wg * CPW + (i >> 2) : wg / WPC2; };
+        auto piece_plane = [&](int i) { return WPC2 == 1 ? 2 * (i & 3) + lpl : (wg % WPC2) * (8 / WPC2) + 2 * i + lpl; };
+        const __nv_bfloat16* rows_base = yx_tile + (size_t)(crank * SUB_ROWS + lrow) * PLANE_ELEMS;
+        auto piece_src = [&](int i) { return rows_base + (size_t)(piece_chunk(i) * 8 + piece_plane(i)) * PSTRIDE; };
+        const int gq = (wg * 4) / GROUP_WARPS;                  // chunk quarter this warp's chunks belong to (warps 2q, 2q+1)
+
+        // ---- epilogue geometry ----
+        const int q = wg & 3, half = wg >> 2;                 // TMEM lane quarter (= warp % 4); column half (16 utterances)
+        const int R = q * 32 + lane;                          // gate row of this CTA = TMEM lane
+        const int gj = lane & 3;                              // gate of this lane: 0=i 1=f 2=g 3=o
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(2 * g * SUB_N + half * CPT2);   // K half 1: + SUB_N
+        const float act_s = gj == 2 ? 2.0f : 1.0f, act_o = gj == 2 ? -1.0f : 0.0f;
+        const uint32_t gt_smem = ptx::smem_u32(sGT) + (uint32_t)(g * GT_BYTES + wg * (16 * 32 * 4));   // this warp's transpose tile
+        float c[CPT2 / 4];
+#pragma unroll
+        for (int k = 0; k < CPT2 / 4; ++k) c[k] = 0.0f;
+        const uint32_t gx_smem0 = ptx::smem_u32(sGx) + (uint32_t)(g * 2 * GXB);
+        // Gx_t staging, one step ahead: the block of step t is copied into buffer t & 1 while step t-1 runs (the copies come from
+        // HBM: issued in their own step they would not be back before the MMAs of a 32-wide sub-tile are).  WARP-PRIVATE: a warp
+        // copies exactly the [16 utterances of its half] x [32 gate rows of its lane quarter] block its own lanes read, so the
+        // hand-over needs a __syncwarp, not a barrier of the group.  One commit group per step (an empty one past the end), so
+        // "all but the newest group" is always "this step's block".  The row index t / gx_div is kept incrementally.
+        int gx_row = 0, gx_left = a.gx_div;       // row of the NEXT block to stage, steps left on that row
+        auto stage_gx = [&](int t) {
+            if (t < a.T) {
+                const size_t toff = (size_t)gx_row * a.gx_st + (size_t)ns * MROWS + (size_t)(q * 32);
+                constexpr int ES = GXH ? 2 : 4, SEGS = 32 * ES / 16;          // 16-byte pieces per utterance of the warp's block: 4 / 8
+                const uint32_t dst = gx_smem0 + (uint32_t)((t & 1) * GXB);
+#pragma unroll
+                for (int i = 0; i < CPT2 * SEGS / 32; ++i) {
+                    const int u = half * CPT2 + lane / SEGS + (32 / SEGS) * i, seg = lane % SEGS;
+                    const int b = b0 + u < a.B ? b0 + u : a.B - 1;
+                    cp_async16(dst + (uint32_t)((u * MROWS + q * 32) * ES + seg * 16),
+                               reinterpret_cast<const char*>(a.Gx) + ((size_t)b * a.gx_sb + toff) * ES + seg * 16);
+                }
+                if (--gx_left == 0) { ++gx_row; gx_left = a.gx_div; }
+            }
+            cp_async_commit();
+        };
+        uint32_t gx_smem = gx_smem0;
+        auto gx_at = [&](int k) -> float {
+            if constexpr (GXH) {
+                uint16_t hbits;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hbits) : "r"(gx_smem + (uint32_t)(((half * CPT2 + k) * MROWS + R) * 2)));
+                return __half2float(__ushort_as_half(hbits));
+            } else {
+                return ld_shared_f32(gx_smem + (uint32_t)(((half * CPT2 + k) * MROWS + R) * 4));
+            }
+        };
+        stage_gx(0);
+        stage_gx(1);
+
+        for (int t = 0; t < a.T; ++t) {
+            gx_smem = gx_smem0 + (uint32_t)((t & 1) * GXB);
+            if (t >= 1) {
+                // ---- h_{t-1} of this sub-tile: L2 -> registers (poll) -> swizzled operand tile ----
+                const size_t soff = (size_t)(t - 1) * step_elems;
+                if (tg == 0) AVC_TRACE2(g, 0);
+                uint4 v[NP];
+#pragma unroll
+                for (int i = 0; i < NP; ++i) v[i] = ld_strong(piece_src(i) + soff);
+                for (uint32_t spin = 0;; ++spin) {          // pieces not written yet: fetch all of them again, together
+                    bool missing = false;
+#pragma unroll
+                    for (int i = 0; i < NP; ++i)
+                        if (unwritten(v[i])) { v[i] = ld_strong(piece_src(i) + soff); missing = true; }
+                    if (!missing) break;
+                    if (spin > (1u << 22)) {
+                        printf("autovc_b200: lstm h poll timed out (slice %d tile %d sub %d t %d warp %d lane %d)\n", ns, bt, g, t, wg, lane);
+                        __trap();
+                    }
+                }
+                if (tg == 0) AVC_TRACE2(g, 1);
+#pragma unroll
+                for (int i = 0; i < NP; ++i) {
+                    const int pl = piece_plane(i);
+                    st_shared_v4(sH_g + (uint32_t)(piece_chunk(i) * HBLK2 + lrow * 128 + ((pl ^ (lrow & 7)) << 4)), v[i]);
+                }
+                ptx::fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive_cluster(&gfull[g * 4 + gq], 0u);     // the LEADER's barrier (both CTAs arrive)
+                if (tg == 0) AVC_TRACE2(g, 2);
+                if (lane == 0) AVC_TRACE2(g, 16 + wg);
+                stage_gx(t + 1);
+            }
+            // ---- epilogue: gates, cell state, h_t ----
+            if (tg == 0) AVC_TRACE2(g, 24);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");     // own pieces of Gx_t (the newest group is Gx_{t+1}) ...
+            __syncwarp();                                            // ... and the other lanes' (the block is this warp's alone)
+            if (tg == 0) AVC_TRACE2(g, 26);
+            float act[CPT2];
+            if (t >= 1) {
+                ptx::mbar_wait(my_acc, (uint32_t)(t - 1) & 1);
+                if (tg == 0) AVC_TRACE2(g, 3);
+                ptx::tc_fence_after();
+                uint32_t acc0[16], acc1[16];
+                ptx::tmem_ld16(taddr, acc0);
+                ptx::tmem_ld16(taddr + (uint32_t)SUB_N, acc1);
+                ptx::tmem_ld_wait();
+                ptx::tc_fence_before();
+                if (tg == 0) AVC_TRACE2(g, 5);
+#pragma unroll
+                for (int k = 0; k < CPT2; ++k) act[k] = __uint_as_float(acc0[k]) + __uint_as_float(acc1[k]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < CPT2; ++k) act[k] = 0.0f;
+            }
+            // gate activation of this lane's row (x' already is the tanh argument, see pack_lstm), written to the warp's transpose
+            // tile [column][gate row]: the four gates of a unit are four consecutive floats there
+            if (a.approx) {
+                const float ps = gj == 2 ? 1.0f : 0.5f, po = gj == 2 ? 0.0f : 0.5f;
+#pragma unroll
+                for (int k = 0; k < CPT2; ++k) {
+                    const float x = act[k] + gx_at(k);
+                    float th;
+                    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(x));
+                    act[k] = fmaf(ps, th, po);
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < CPT2; ++k) {
+                    const float x = act[k] + gx_at(k);
+                    act[k] = __fdividef(act_s, 1.0f + __expf(-2.0f * x)) + act_o;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < CPT2; ++k)      // after ALL the loads above: a store in the loop would order every Gx read behind it
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(gt_smem + (uint32_t)((k * 32 + lane) * 4)), "f"(act[k]) : "memory");
+            __syncwarp();
+            if (tg == 0) AVC_TRACE2(g, 6);
+            // lane j: unit (j >> 2) of this quarter, columns 4 (j & 3) .. + 3 of this half: i, f, g, o as one 16-byte read each
+            constexpr int H2 = CPT2 / 4;
+            uint32_t hp[H2 / 2];
+#pragma unroll
+            for (int k = 0; k < H2; k += 2) {
+                float hv[2];
+#pragma unroll
+                for (int w = 0; w < 2; ++w) {
+                    const int kk = k + w;
+                    const uint4 gates = ld_shared_v4(gt_smem + (uint32_t)(((gj * H2 + kk) * 32 + (lane & ~3)) * 4));
+                    const float ig = __uint_as_float(gates.x), fg = __uint_as_float(gates.y), gg = __uint_as_float(gates.z), og = __uint_as_float(gates.w);
+                    c[kk] = cell_update(fg, c[kk], ig, gg);
+                    float tc;
+                    if (a.approx) asm("tanh.approx.f32 %0, %1;" : "=f"(tc) : "f"(c[kk]));
+                    else tc = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * c[kk]));
+                    hv[w] = og * tc;
+                }
+                __nv_bfloat162 h2 = __floats2bfloat162_rn(hv[0], hv[1]);
+                hp[k >> 1] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            __syncwarp();        // the tile is rewritten by the next step's activations
+            if (tg == 0) AVC_TRACE2(g, 7);
+            // h_t out, straight from registers.  The lane holds one unit x four utterances (hp[0] = columns 0,1; hp[1] = columns 2,3
+            // of its block); lanes j and j ^ 4 hold neighbouring units of the same utterances.  One exchange gives every lane a
+            // (unit pair) x (two utterances) block, i.e. two 32-bit words: the validity protocol needs whole 32-bit words from one
+            // thread (a word with one stale half would not read as "unwritten").  No shared-memory staging, no barrier.
+            {
+                const bool odd = (lane >> 2) & 1;
+                const uint32_t mine = odd ? hp[1] : hp[0];
+                const uint32_t theirs = __shfl_xor_sync(0xffffffffu, odd ? hp[0] : hp[1], 4);
+                const uint32_t ev = odd ? theirs : mine, od = odd ? mine : theirs;      // even unit / odd unit, same two utterances
+                const uint32_t w0 = __byte_perm(ev, od, 0x5410), w1 = __byte_perm(ev, od, 0x7632);
+                const int col = half * CPT2 + gj * H2 + (odd ? 2 : 0);                  // first of the two utterances (within the sub-tile)
+                const int upair = (lane >> 3) * 2;                                       // even unit of the pair, within this quarter's 8
+                __nv_bfloat16* yx = yx_tile + (size_t)t * step_elems + ((size_t)(ns * 4 + q) * SUB_N + col) * PLANE_ELEMS + upair;
+                if (t + 1 < a.T) {
+                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx), "r"(w0) : "memory");
+                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx + PLANE_ELEMS), "r"(w1) : "memory");
+                }
+                __nv_bfloat16* y = a.Y + (size_t)t * a.y_st + (size_t)ns * SLICE_UNITS + q * 8 + upair;
+                if (b0 + col < a.B) *reinterpret_cast<uint32_t*>(y + (size_t)(b0 + col) * a.y_sb) = w0;
+                if (b0 + col + 1 < a.B) *reinterpret_cast<uint32_t*>(y + (size_t)(b0 + col + 1) * a.y_sb) = w1;
+            }
+            if (tg == 0) AVC_TRACE2(g, 4);
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();
+    if (warp == 0) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+    }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -502,6 +887,18 @@ const void* kernel_for_tn(int nkb, bool gxh) {
 }
 const void* kernel_for(int nkb, bool gxh, int tn) { return tn == 32 ? kernel_for_tn<32>(nkb, gxh) : kernel_for_tn<64>(nkb, gxh); }
 
+const void* kernel_for2(int nkb, bool gxh) {
+    switch (nkb) {
+        case 16: return gxh ? (const void*)ll2_lstm_kernel<16, true> : (const void*)ll2_lstm_kernel<16, false>;
+        case 8: return gxh ? (const void*)ll2_lstm_kernel<8, true> : (const void*)ll2_lstm_kernel<8, false>;
+        default: return gxh ? (const void*)ll2_lstm_kernel<4, true> : (const void*)ll2_lstm_kernel<4, false>;
+    }
+}
+int smem_for2(int nkb, bool gxh) {
+    const int nkb_s = nkb > p2::MAX_TMEM_CHUNKS2 ? nkb - p2::MAX_TMEM_CHUNKS2 : 0;
+    return nkb_s * W_BLK_BYTES + 2 * nkb * p2::HBLK2 + 4 * p2::gx2_bytes(gxh) + 2 * p2::GT_BYTES + 1024 + 512;
+}
+
 int smem_for(int nkb) {
     const int nkb_s = nkb > MAX_TMEM_CHUNKS ? nkb - MAX_TMEM_CHUNKS : 0;
     return nkb_s * W_BLK_BYTES + nkb * H_BLK_BYTES + GX_BYTES + HT_BYTES + 1024 + 512;
@@ -514,6 +911,7 @@ struct LlLstmPlan {
     std::vector<LlLstmArgs> args;
     std::vector<dim3> grids;
     int nkb, tn;
+    bool pipelined;           // ll2_lstm_kernel: two 32-utterance sub-tiles per CTA pair
     bool gx_f16;
     int smem_bytes;
     void* yx_base; size_t yx_bytes;       // region to pre-fill with the "unwritten" pattern before every launch
@@ -529,6 +927,12 @@ const char* ll_lstm_init() {
         if (cudaFuncSetAttribute(kernel_for(4 << ((i >> 1) % 3), i & 1, i < 6 ? 64 : 32), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  smem_for(4 << ((i >> 1) % 3))) != cudaSuccess)
             return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed for ll_lstm_kernel";
+    for (int i = 0; i < 6; ++i) {
+        const int bytes = smem_for2(4 << (i >> 1), i & 1);
+        if (bytes > 227 * 1024) continue;          // H = 1024 with fp32 Gx does not fit: that plan takes the one-tile kernel
+        if (cudaFuncSetAttribute(kernel_for2(4 << (i >> 1), i & 1), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
+            return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed for ll2_lstm_kernel";
+    }
     g_encode_ll = reinterpret_cast<EncodeTiledFn>(fn);
     return nullptr;
 }
@@ -551,6 +955,13 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
     // tile width: 32 utterances per CTA pair when twice the tiles still fit the machine (small batches: shorter steps)
     int tn = ceil_div(B, 32) * G_n <= (num_sms & ~1) ? 32 : 64;
     if (const char* tv = getenv("AVC_LSTM_TN")) tn = atoi(tv) == 32 ? 32 : 64;
+    // Batches that would take 64-wide tiles run as two pipelined 32-wide sub-tiles per CTA pair instead (ll2_lstm_kernel): one
+    // sub-tile's exchange latency hides behind the other's MMAs and epilogue.  AVC_LSTM_P2=0/1 forces the choice (A/B aid).
+    bool pipelined = tn == 64;
+    if (const char* pv = getenv("AVC_LSTM_P2")) pipelined = atoi(pv) != 0;
+    if (pipelined && smem_for2(nkb, plan->gx_f16) > 227 * 1024) pipelined = false;     // H = 1024 with fp32 Gx (AVC_GX_F32): no room for the second Gx buffer
+    plan->pipelined = pipelined;
+    if (pipelined) { tn = 64; plan->smem_bytes = smem_for2(nkb, plan->gx_f16); }
     plan->tn = tn;
     plan->yx_base = Yx; plan->yx_bytes = (size_t)T * ceil_div(B, tn) * tn * H * 2;
     {
@@ -575,13 +986,14 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         a.Y = reinterpret_cast<__nv_bfloat16*>(Y) + (size_t)bs * a.y_sb;
         a.Yx = reinterpret_cast<__nv_bfloat16*>(Yx);
         a.tiles = ceil_div(B, tn); a.tile0 = bs / tn;
+        if (pipelined) { a.tiles *= 2; a.tile0 *= 2; }           // Yx is indexed in 32-row tiles
         a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
         // canary poll of the loader-only warps: worth 10 % at H = 1024 with a full grid (without it they hammer the fabric with
         // 64 KiB waves per CTA while the epilogue runs); at H <= 512 (16 KiB waves) and on small grids it only adds a round trip
         // per step (lstm1 at B = 256: 0.328 -> 0.308 ms; at B <= 32: 0.313 -> 0.287 ms)
         { const char* cv = getenv("AVC_LSTM_CANARY"); a.canary = cv ? atoi(cv) : (H <= 512 || G_n * ceil_div(Bc, tn) <= 16 ? 0 : 1); }
         { const char* gv = getenv("AVC_LSTM_GX_LATE"); a.gx_late = gv ? atoi(gv) : 1; }
-        a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, tn);          // the pair's MMA: M = 256 (128 gate rows per CTA), N = tile width
+        a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, pipelined ? p2::SUB_N : tn);   // the pair's MMA: M = 256 (128 gate rows per CTA), N = tile width
         plan->args.push_back(a);
         plan->grids.push_back(dim3(G_n, ceil_div(Bc, tn)));
     }
@@ -593,23 +1005,41 @@ void ll_lstm_plan_destroy(LlLstmPlan* plan) { delete plan; }
 cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches) {
     static long long* d_trace = nullptr;
     const bool tracing = getenv("AVC_LSTM_TRACE") != nullptr;
-    if (tracing && !d_trace) cudaMalloc(&d_trace, sizeof(long long) * (TRACE_STEPS + 1) * TRACE_PTS);
+    if (tracing && !d_trace) cudaMalloc(&d_trace, sizeof(long long) * TRACE_WORDS);
     // "unwritten" pattern: every 16-bit element = 0xFFFF
     cudaError_t e = cudaMemsetAsync(plan->yx_base, 0xFF, plan->yx_bytes, s);
     if (e != cudaSuccess) return e;
     for (size_t i = 0; i < plan->args.size(); ++i) {
         LlLstmArgs args = plan->args[i];
         args.trace = tracing ? d_trace : nullptr;
-        if (tracing) cudaMemsetAsync(d_trace, 0, sizeof(long long) * (TRACE_STEPS + 1) * TRACE_PTS, s);
+        if (tracing) cudaMemsetAsync(d_trace, 0, sizeof(long long) * TRACE_WORDS, s);
         void* kargs[2] = {(void*)&plan->tmW, (void*)&args};
         // CTAs wait on one another's output: cooperative launch (guaranteed co-residency), with the checked non-cooperative
         // retry of launch_persistent() for profilers (AVC_LSTM_NOCOOP forces it)
-        e = launch_persistent(kernel_for(plan->nkb, plan->gx_f16, plan->tn), plan->grids[i], dim3(NUM_THREADS), (size_t)plan->smem_bytes, 2,
-                              kargs, s, getenv("AVC_LSTM_NOCOOP") != nullptr);
+        e = launch_persistent(plan->pipelined ? kernel_for2(plan->nkb, plan->gx_f16) : kernel_for(plan->nkb, plan->gx_f16, plan->tn), plan->grids[i],
+                              dim3(plan->pipelined ? p2::THREADS : NUM_THREADS), (size_t)plan->smem_bytes, 2, kargs, s,
+                              getenv("AVC_LSTM_NOCOOP") != nullptr);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
-        if (tracing) {   // debugging aid: synchronous dump of the per-step timeline of CTA (0,0)
-            long long hbuf[(TRACE_STEPS + 1) * TRACE_PTS];
+        if (tracing && plan->pipelined) {
+            long long hbuf[TRACE_WORDS];
+            cudaStreamSynchronize(s);
+            cudaMemcpy(hbuf, d_trace, sizeof hbuf, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "ll2_lstm trace H=%d B=%d grid=(%d,%d): per sub-tile, cycles since its loads were issued (warp 0 of the group unless noted): landed published | "
+                    "quarters ready q0..q3 (issuers), committed | Gx wait entered, Gx ready | acc_seen tmem_read gates cell stored | publish time of warps 0..7 || absolute start\n",
+                    args.H, args.B, plan->grids[i].x, plan->grids[i].y);
+            const long long t00 = hbuf[0];
+            for (int st = 0; st < TRACE_STEPS; ++st)
+                for (int g = 0; g < 2; ++g) {
+                    const long long* r = hbuf + (st * 2 + g) * p2::TR_PTS;
+                    if (!r[0]) continue;
+                    const long long z = r[0];
+                    fprintf(stderr, "  t=%d sub %d: %5lld %5lld | %5lld %5lld %5lld %5lld, %5lld | %5lld %5lld | %5lld %5lld %5lld %5lld %5lld | %5lld %5lld %5lld %5lld %5lld %5lld %5lld %5lld || %7lld\n",
+                            TRACE_T0 + st, g, r[1] - z, r[2] - z, r[10] - z, r[11] - z, r[12] - z, r[13] - z, r[9] - z, r[24] - z, r[26] - z, r[3] - z, r[5] - z, r[6] - z, r[7] - z, r[4] - z,
+                            r[16] - z, r[17] - z, r[18] - z, r[19] - z, r[20] - z, r[21] - z, r[22] - z, r[23] - z, z - t00);
+                }
+        } else if (tracing) {   // debugging aid: synchronous dump of the per-step timeline of CTA (0,0)
+            long long hbuf[TRACE_WORDS];
             cudaStreamSynchronize(s);
             cudaMemcpy(hbuf, d_trace, sizeof hbuf, cudaMemcpyDeviceToHost);
             fprintf(stderr, "ll_lstm trace H=%d B=%d grid=(%d,%d): cycles since warp 0 saw its canary: "

@@ -179,25 +179,65 @@ class VoiceConverter:
         if self._pipe is None:
             self._pipe = HostPipeline(self.AE, self.device)
 
+        # Speaker embeddings: one table row per DISTINCT tensor object (the cache hands out one tensor per speaker), gathered
+        # per batch with one index_select into pinned staging instead of stacking 2 x max_batch small tensors.
+        table_rows: Dict[int, int] = {}
+        table: List[torch.Tensor] = []
+        def row_of(t: torch.Tensor) -> int:
+            r = table_rows.get(id(t))
+            if r is None:
+                r = table_rows[id(t)] = len(table)
+                table.append(t.detach().to(torch.float32).reshape(-1))
+            return r
+        src_rows = [row_of(t) for t in c_src]
+        trg_rows = [row_of(t) for t in c_trg]
+        emb = torch.stack(table)
+        pin = torch.cuda.is_available()
+
+        def gather(rows: List[int]) -> torch.Tensor:
+            out_ = torch.empty((len(rows), emb.shape[1]), dtype=torch.float32, pin_memory=pin)
+            torch.index_select(emb, 0, torch.tensor(rows, dtype=torch.int64), out=out_)
+            return out_
+
         class _Staged:      # batch i is staged when the pipeline enqueues its copy, i.e. while batch i-1 computes
             def __len__(_s):
                 return len(plan)
 
             def __getitem__(_s, i):
                 sel = plan[i]
-                return (host_rows([mels[k] for k in sel]), host_rows([c_src[k] for k in sel]), host_rows([c_trg[k] for k in sel]))
+                return (host_rows([mels[k] for k in sel]), gather([src_rows[k] for k in sel]), gather([trg_rows[k] for k in sel]))
 
         if output == "host":
-            slabs = [torch.empty((len(sel),) + tuple(mels[sel[0]].shape), dtype=torch.float32, pin_memory=True) for sel in plan]
-            self._pipe.run(_Staged(), [(None, slab, None) for slab in slabs])
+            # one pinned result tensor per length bucket; the per-utterance views are cut (one unbind per batch) while the
+            # pipeline is running, not after it
+            slabs: Dict[Tuple[int, ...], torch.Tensor] = {}
+            fill: Dict[Tuple[int, ...], int] = {}
+            for sel in plan:
+                shp = tuple(mels[sel[0]].shape)
+                fill[shp] = fill.get(shp, 0) + len(sel)
+            for shp, n_rows in fill.items():
+                slabs[shp] = torch.empty((n_rows,) + shp, dtype=torch.float32, pin_memory=pin)
+                fill[shp] = 0
+            outs = []
+            for sel in plan:
+                shp = tuple(mels[sel[0]].shape)
+                part = slabs[shp][fill[shp]:fill[shp] + len(sel)]
+                fill[shp] += len(sel)
+                outs.append((None, part, None))
+            staged = _Staged()
+
+            class _Outs:      # indexing batch i's outputs (the pipeline does so right after launching batch i) also cuts its views
+                def __getitem__(_s, i):
+                    for k, v in zip(plan[i], outs[i][1].unbind(0)):
+                        out[k] = v
+                    return outs[i]
+
+            self._pipe.run(staged, _Outs())
             self._pipe.d2h_stream.synchronize()
-            for sel, slab in zip(plan, slabs):
-                for j, i in enumerate(sel):
-                    out[i] = slab[j]
         else:
             def keep(bi, res):
-                for j, i in enumerate(plan[bi]):
-                    out[i] = res[1][j]
+                for k, v in zip(plan[bi], res[1].unbind(0)):
+                    out[k] = v
             self._pipe.run(_Staged(), None, on_result=keep)
         return out
 

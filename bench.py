@@ -469,7 +469,11 @@ def main():
         vc = VoiceConverter(model, embed_speaker=se.as_embed_fn(), device=dev, max_batch=B)
         mine_keys = [u.speaker for u in srcs[lo:hi]] + [u.speaker for u in trgs[lo:hi]]
         mine_data = [u.speaker_data for u in srcs[lo:hi]] + [u.speaker_data for u in trgs[lo:hi]]
-        vc.learn_speakers(mine_keys[:1], mine_data[:1], embed_many=se.embed_speakers)    # warm-up of the speaker-encoder path
+        # untimed passes first: the speaker encoder's workspace / plans for this batch of partials, and torch's caching HOST allocator,
+        # which needs a few rounds before the 168 MB pinned result block of a pass is recycled instead of cudaHostAlloc'ed (~100 ms)
+        vc.learn_speakers(mine_keys, mine_data, embed_many=se.embed_speakers)
+        for _ in range(3):
+            vc.convert_multiple(srcs, trgs, match_method="align", distributed=world > 1, gather=False, output="host")
         vc.speakers.clear()
         vc.embed_calls = 0
         barrier()
@@ -477,7 +481,6 @@ def main():
         a0.record()
         n_emb = vc.learn_speakers(mine_keys, mine_data, embed_many=se.embed_speakers)     # ONE batched call, once per speaker
         a1.record()
-        vc.convert_multiple(srcs, trgs, match_method="align", distributed=world > 1, gather=False, output="host")   # warm-up pass
         barrier()
         flush.zero_()
         barrier()

@@ -295,11 +295,12 @@ def test_weight_changes_reach_the_packed_copy():
     x, c_org, c_trg = (t.cuda() for t in synth_inputs(2, 64, seed=2))
     base = m(x, c_org, c_trg)[1].clone()
     w = m.decoder.linear_projection.linear_layer.bias
+    saved = w.detach().clone()
     with torch.no_grad():
         w.add_(0.5)
     shifted = m(x, c_org, c_trg)[1]
     assert float((shifted - base).abs().max()) > 0.1
-    w.data.sub_(0.5)                        # invisible to the version counter ...
+    w.data.copy_(saved)                     # invisible to the version counter ...
     assert torch.equal(m(x, c_org, c_trg)[1], shifted)
     m.invalidate()                          # ... until the caller says so
     assert float((m(x, c_org, c_trg)[1] - base).abs().max()) <= 1e-6

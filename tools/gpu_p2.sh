@@ -1,0 +1,16 @@
+#!/bin/bash
+# pipelined recurrence: parity subset, A/B of the phase times, step trace
+mkdir -p gpurun_out
+echo "== parity subset"; timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_speaker_encoder.py -m gpu -q -x -k "not stress and not config3" 2>&1 | tail -6
+for cfg in ${CFGS:-"AVC_LSTM_P2=0" "AVC_LSTM_P2=1"}; do
+  for rep in 1 2; do
+    echo "--- $cfg"; env $cfg timeout 600 python bench.py --no-configs --no-cpu-baseline --steps 20 2>&1 | python -c "
+import sys,json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d=json.loads(l); print(round(d['ms_per_step'],4), d['phase_ms'], 'p50', round(d['latency_p50_ms_b1_t128'],3), 'e2e', round(d['e2e']['value']/1e6,2))
+    elif 'rror' in l: print(l.strip()[:300])
+"
+  done
+done
+echo "== trace (lstm2 layers)"; env AVC_LSTM_TRACE=1 PW=1 PK=1 timeout 300 python tools/profile_step.py 2>&1 | grep -A17 "ll2_lstm trace" | tail -18
