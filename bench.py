@@ -472,8 +472,10 @@ def main():
         # untimed passes first: the speaker encoder's workspace / plans for this batch of partials, and torch's caching HOST allocator,
         # which needs a few rounds before the 168 MB pinned result block of a pass is recycled instead of cudaHostAlloc'ed (~100 ms)
         vc.learn_speakers(mine_keys, mine_data, embed_many=se.embed_speakers)
-        for _ in range(3):
-            vc.convert_multiple(srcs, trgs, match_method="align", distributed=world > 1, gather=False, output="host")
+        out4 = {(80, T4): torch.empty(hi - lo, 80, T4).pin_memory()}      # the serving loop's own result buffer, reused from call to call
+        c4_args = dict(match_method="align", distributed=world > 1, gather=False, output="host", host_buffers=out4)
+        for _ in range(2):
+            vc.convert_multiple(srcs, trgs, **c4_args)
         vc.speakers.clear()
         vc.embed_calls = 0
         barrier()
@@ -485,7 +487,7 @@ def main():
         flush.zero_()
         barrier()
         s1.record()
-        res = vc.convert_multiple(srcs, trgs, match_method="align", distributed=world > 1, gather=False, output="host")
+        res = vc.convert_multiple(srcs, trgs, **c4_args)
         s2.record()
         barrier()
         assert sum(r is not None for r in res) == hi - lo and vc.embed_calls == n_emb
@@ -497,7 +499,7 @@ def main():
                                  "h2d_bytes": (hi - lo) * (80 * T4 + 512) * 4, "d2h_bytes": (hi - lo) * 80 * T4 * 4},
                          "speaker_encoder": {"ms": se_ms, "speakers_per_rank": n_emb, "partials_per_speaker": 8,
                                              "note": "all speakers of a rank in one batched SpeakerEncoder.embed_speakers call, outside the convert timing"}}
-        del slab, srcs, trgs, res
+        del slab, srcs, trgs, res, out4
 
     if rank == 0:
         peaks, peak_src = load_peaks()
