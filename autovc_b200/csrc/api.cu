@@ -42,7 +42,10 @@ enum LayerId {
     L_SE_L0_IH = L_GEN_COUNT, L_SE_L0_HH, L_SE_L1_IH, L_SE_L1_HH, L_SE_L2_IH, L_SE_L2_HH, L_SE_LINEAR,
     // the 11 convolutions again WITHOUT the BatchNorm folded in, for the train-mode (batch statistics) forward
     L_RAW_CONV0, L_RAW_COUNT_END = L_RAW_CONV0 + 11,
-    L_COUNT = L_RAW_COUNT_END
+    // encoder conv0 split for the fused speaker concat (reference encoder.py:65-66): the 80 mel channels as a 5-tap convolution,
+    // the dim_emb speaker channels as a plain GEMM per tap whose result enters conv0's epilogue as a per-utterance bias
+    L_ENC_CONV0_MEL = L_RAW_COUNT_END, L_ENC_CONV0_SPK,
+    L_COUNT
 };
 
 constexpr int N_BN = 11;   // BatchNorm layers in path order: encoder 0-2, decoder 0-2, postnet 0-4
@@ -63,6 +66,7 @@ const char* kLayerNames[L_COUNT] = {
     "se.lstm.l0.ih", "se.lstm.l0.hh", "se.lstm.l1.ih", "se.lstm.l1.hh", "se.lstm.l2.ih", "se.lstm.l2.hh", "se.linear",
     "raw.enc.conv0", "raw.enc.conv1", "raw.enc.conv2", "raw.dec.conv0", "raw.dec.conv1", "raw.dec.conv2",
     "raw.post.conv0", "raw.post.conv1", "raw.post.conv2", "raw.post.conv3", "raw.post.conv4",
+    "enc.conv0.mel", "enc.conv0.spk",
 };
 
 struct Workspace {
@@ -70,11 +74,12 @@ struct Workspace {
     char* X0; char* actA; char* actB; float* GxE; char* Y0; float* Y1; float* cstate;
     char* Dm; float* Gd1; char* H1; float* G2; char* H2a; char* H2b; char* melc;
     char* Yb;    // exchange copy of the running LSTM layer's output (ll_lstm.cu)
+    char* Cb; float* Sspk; float* Espk;   // fused speaker concat: c_org in bf16 [B][E], per-tap products [B][5][512], edge-class bias vectors [B][5][512]
     double* bn_partial; float* bn_ss;   // train-mode BatchNorm scratch (batchnorm.cu); the fp32 conv rows reuse G2
     size_t total;
 };
 
-// mode: 0 forward, 1 encode only, 2 speaker encoder, 3 / 4 forward / encode with batch-statistics BatchNorm
+// mode: 0 forward, 1 encode only, 2 speaker encoder, 3 / 4 forward / encode with batch-statistics BatchNorm; + 8: conv0 over the materialised concat
 struct PlanSet {
     void* ws = nullptr; int B = 0, T = 0, mode = 0;
     uint64_t stamp = 0;
@@ -191,6 +196,22 @@ bool pack_conv(avc_ctx* h, Layer& L, const std::string& prefix, int cin, int cou
     return true;
 }
 
+// Encoder conv0 split along the input channels (fused speaker concat): `mel` = channels [0, 80) as a 5-tap convolution
+// [Cout][5*128], `spk` = channels [80, 80+E) as a plain matrix [5*Cout][E] (row tap*Cout + n), both with the BatchNorm scale
+// folded in; the folded bias stays with the edge-class vectors (speaker_edge_kernel).  Built from the packed full layer.
+void split_conv0(const Layer& F, Layer& M, Layer& S, int n_mels, int E) {
+    M.taps = KTAPS; M.Cin = n_mels; M.Cp = round_up(n_mels, 64); M.N = F.N; M.K = KTAPS * M.Cp; M.Kp = M.K;
+    M.w.assign((size_t)M.N * M.Kp, 0.0f); M.b = F.b;
+    S.taps = 1; S.Cin = E; S.Cp = E; S.N = KTAPS * F.N; S.K = E; S.Kp = E;
+    S.w.assign((size_t)S.N * S.Kp, 0.0f); S.b.assign(S.N, 0.0f);
+    for (int n = 0; n < F.N; ++n)
+        for (int tap = 0; tap < KTAPS; ++tap) {
+            const float* src = &F.w[(size_t)n * F.Kp + tap * F.Cp];
+            for (int c = 0; c < n_mels; ++c) M.w[(size_t)n * M.Kp + tap * M.Cp + c] = src[c];
+            for (int c = 0; c < E; ++c) S.w[(size_t)(tap * F.N + n) * S.Kp + c] = src[n_mels + c];
+        }
+}
+
 // nn.LSTM matrices -> unit-major gate rows: packed row d*4H + u*4 + g  <-  PyTorch row g*H + u of direction d.
 // ih: [ndir*4H][K] with bias = b_ih + b_hh;  hh: [ndir*4H][H], no bias.
 // `prescale` (layers that run on the tensor-core recurrence, ll_lstm.cu): the rows of the sigmoid gates (i, f, o) of W_ih, W_hh
@@ -294,6 +315,9 @@ Workspace carve(const avc_ctx* h, char* base, int B, int T) {
     w.H2b = take(M * LSTM2_H * as);
     w.melc = take(M * N_MELS * as);
     w.Yb = take(ll_lstm_exchange_bytes(B, T, hmax));
+    w.Cb = take((size_t)B * d.dim_emb * 2);
+    w.Sspk = (float*)take((size_t)B * KTAPS * CONV_CH * 4);
+    w.Espk = (float*)take((size_t)B * KTAPS * CONV_CH * 4);
     w.bn_partial = (double*)take((size_t)bn_partial_capacity((int)M) * 2 * BN_MAX_CH * sizeof(double));
     w.bn_ss = (float*)take((size_t)2 * BN_MAX_CH * sizeof(float));
     w.total = off;
@@ -334,7 +358,7 @@ struct Runner {
     // out[m,n] = act(A W^T + b); A is an activation buffer of `a_type`
     int last_stat_chunks = 0;   // set by gemm(): > 0 when the launch also wrote the BatchNorm column sums
     void gemm(int lid, const void* A, int a_type, int lda, int M, int Tutt, int act, void* out, int out_type, int ldo,
-              float* out_t = nullptr, const float* res_t = nullptr, double* stat_partial = nullptr) {
+              float* out_t = nullptr, const float* res_t = nullptr, double* stat_partial = nullptr, const float* row_bias = nullptr) {
         if (!ok()) return;
         const Layer& L = h->layers[lid];
         mark(L.taps > 1 ? AVC_PHASE_CONV : AVC_PHASE_PROJ);
@@ -343,7 +367,7 @@ struct Runner {
         p.M = M; p.N = L.N; p.K = L.Kp; p.T = Tutt;
         p.taps = L.taps; p.Cin = L.Cin; p.Cp = L.Cp;
         p.W = L.w_dev; p.w_type = L.w_type; p.ldw = L.Kp;
-        p.bias = L.b_dev; p.act = act;
+        p.bias = row_bias ? nullptr : L.b_dev; p.row_bias = row_bias; p.act = act;
         p.out = out; p.out_type = out_type; p.ldo = ldo;
         p.out_t = out_t; p.res_t = res_t;
         p.stat_partial = stat_partial; p.stat_capacity = stat_partial ? bn_partial_capacity(M) : 0;
@@ -493,7 +517,8 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
     Runner r{h, (cudaStream_t)stream, B, T};
     r.wsp = &w;
     r.bn_train = bn_train; r.bn_stats = bn_stats;
-    const int mode = (encode_only ? 1 : 0) + (bn_train ? 3 : 0);
+    const bool fused_concat = !bn_train && !getenv("AVC_NO_FUSED_CONCAT");     // A/B and test aid: the unfused conv0 over the materialised concat
+    const int mode = (encode_only ? 1 : 0) + (bn_train ? 3 : 0) + (fused_concat ? 0 : 8);
     h->launches = 0;
     for (auto ev : h->prof_events) cudaEventDestroy(ev);
     h->prof_events.clear(); h->prof_cats.clear();
@@ -508,8 +533,20 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
 
     // ---- encoder (reference encoder.py:53-97) ----
     r.mark(AVC_PHASE_LAYOUT);
-    r.check(launch_pack_input(x, c_org, w.X0, at, B, T, E, r.s), "pack_input"); h->launches++;
-    r.conv_bn(0, w.X0, at, N_MELS + E, M, T, ACT_RELU, w.actA, at, CONV_CH);
+    if (r.use_tc() && fused_concat && T >= 4) {
+        // Fused speaker concat (reference encoder.py:65-66): cat(x, c_org expanded over t) is never built.  conv0 runs over the 80 mel
+        // channels only (K = 5 x 128 instead of 5 x 384); the speaker channels' share - constant in t but for the frames whose window
+        // reaches into the zero padding - is one [B, E] x [E, 5 x 512] GEMM and enters conv0's epilogue as a per-utterance bias.
+        r.check(launch_pack_input(x, c_org, w.X0, at, B, T, 0, r.s), "pack_input (mel)"); h->launches++;
+        r.check(launch_cast_pad_rows(c_org, w.Cb, at, B, E, E, r.s), "cast c_org"); h->launches++;
+        r.gemm(L_ENC_CONV0_SPK, w.Cb, at, E, B, 1, ACT_NONE, w.Sspk, DT_F32, KTAPS * CONV_CH);
+        r.mark(AVC_PHASE_LAYOUT);
+        r.check(launch_speaker_edge(w.Sspk, h->layers[L_ENC_CONV0_MEL].b_dev, w.Espk, B, CONV_CH, r.s), "speaker edge vectors"); h->launches++;
+        r.gemm(L_ENC_CONV0_MEL, w.X0, at, N_MELS, M, T, ACT_RELU, w.actA, at, CONV_CH, nullptr, nullptr, nullptr, w.Espk);
+    } else {
+        r.check(launch_pack_input(x, c_org, w.X0, at, B, T, E, r.s), "pack_input"); h->launches++;
+        r.conv_bn(0, w.X0, at, N_MELS + E, M, T, ACT_RELU, w.actA, at, CONV_CH);
+    }
     r.conv_bn(1, w.actA, at, CONV_CH, M, T, ACT_RELU, w.actB, at, CONV_CH);
     r.conv_bn(2, w.actB, at, CONV_CH, M, T, ACT_RELU, w.actA, at, CONV_CH);
     r.gemm(L_ENC_L0_IH, w.actA, at, CONV_CH, M, T, ACT_NONE, w.GxE, DT_F32, 8 * dn);
@@ -707,18 +744,24 @@ int avc_load_weights(avc_handle h, const avc_weight_desc* table, int n) {
         if (ok) { bn_gamma[i] = h->raw[std::string(kBnPrefix[i]) + ".1.weight"]; bn_beta[i] = h->raw[std::string(kBnPrefix[i]) + ".1.bias"]; }
     }
     if (!ok) { h->loaded = false; return AVC_ERR_MISSING_WEIGHT; }
+    split_conv0(L[L_ENC_CONV0], L[L_ENC_CONV0_MEL], L[L_ENC_CONV0_SPK], N_MELS, E);
     h->raw.clear();
     for (int i = 0; i < L_GEN_COUNT; ++i) {
         const bool post = i >= L_POST_CONV0;
         L[i].w_type = h->precision == AVC_PREC_FP32 ? DT_F32 : (post ? DT_F16 : DT_BF16);
     }
     for (int i = 0; i < N_BN; ++i) L[L_RAW_CONV0 + i].w_type = L[kBnFolded[i]].w_type;
+    L[L_ENC_CONV0_MEL].w_type = L[L_ENC_CONV0_SPK].w_type = L[L_ENC_CONV0].w_type;
     if (h->device >= 0) {
         DeviceGuard guard;
         cudaError_t e = guard.enter(h->device);
         if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
         drop_plans(h, 0);     // cached generator plans point at the old weight buffers
         for (int i = 0; i < L_GEN_COUNT; ++i) {
+            int rc = upload_layer(h, L[i]);
+            if (rc != AVC_OK) return rc;
+        }
+        for (int i = L_ENC_CONV0_MEL; i <= L_ENC_CONV0_SPK; ++i) {
             int rc = upload_layer(h, L[i]);
             if (rc != AVC_OK) return rc;
         }

@@ -34,6 +34,8 @@ struct GemmParams {
     int w_type;
     int ldw;
     const float* bias;  // [N]
+    const float* row_bias;  // optional (conv layers, tensor-core path): [B][5][N] added per row instead of `bias`; class of frame t:
+                            // 0 interior, 1: t = 0, 2: t = 1, 3: t = T-2, 4: t = T-1  (the fused speaker term of encoder conv0)
     int act;
     void* out;          // row-major [M][ldo] of out_type, or nullptr
     int out_type;

@@ -304,12 +304,37 @@ cudaError_t launch_simt_lstm_step(const LstmStepParams& q, int ndir, cudaStream_
     return cudaGetLastError();
 }
 
+// Encoder conv0's speaker term (reference encoder.py:65-70: the embedding is concatenated on every frame, so its share of the
+// 5-tap convolution is constant in t except where the window reaches into the zero padding).  S[b][tap][n] = sum_c W0'[n, 80+c,
+// tap] c_org[b, c] comes from one small GEMM; this kernel turns it into the five per-utterance bias vectors the conv0 epilogue adds:
+//   E[b][0] interior = bias + S0+S1+S2+S3+S4,   E[b][1] (t = 0) = bias + S2+S3+S4,     E[b][2] (t = 1)   = bias + S1+S2+S3+S4,
+//   E[b][3] (t = T-2) = bias + S0+S1+S2+S3,     E[b][4] (t = T-1) = bias + S0+S1+S2.
+__global__ void speaker_edge_kernel(const float* __restrict__ S, const float* __restrict__ bias, float* __restrict__ E, int B, int N) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * N) return;
+    const int b = i / N, n = i - b * N;
+    const float* s = S + (size_t)b * 5 * N + n;
+    const float s0 = s[0], s1 = s[N], s2 = s[2 * N], s3 = s[3 * N], s4 = s[4 * N], bb = bias[n];
+    float* e = E + (size_t)b * 5 * N + n;
+    const float mid = s1 + s2 + s3;
+    e[0] = bb + (s0 + mid + s4);
+    e[N] = bb + (s2 + s3 + s4);
+    e[2 * N] = bb + (mid + s4);
+    e[3 * N] = bb + (s0 + mid);
+    e[4 * N] = bb + (s0 + s1 + s2);
+}
+
 cudaError_t launch_pack_input(const float* x, const float* c_org, void* X0, int out_type, int B, int T, int E,
                               cudaStream_t s) {
     dim3 grid(ceil_div(T, 32), 1, B), block(32, 8);
     if (out_type == DT_F32) pack_input_kernel<float><<<grid, block, 0, s>>>(x, c_org, (float*)X0, B, T, E);
     else if (out_type == DT_BF16) pack_input_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(x, c_org, (__nv_bfloat16*)X0, B, T, E);
     else pack_input_kernel<__half><<<grid, block, 0, s>>>(x, c_org, (__half*)X0, B, T, E);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_speaker_edge(const float* S, const float* bias, float* E, int B, int N, cudaStream_t s) {
+    speaker_edge_kernel<<<ceil_div(B * N, 256), 256, 0, s>>>(S, bias, E, B, N);
     return cudaGetLastError();
 }
 

@@ -34,6 +34,7 @@ struct TcGemmArgs {
     int tiles_t, tiles_n, num_tiles;
     int T;                               // true frames per utterance (channel-first output addressing)
     const float* bias;
+    const float* row_bias;               // [B][5][N] per-row bias (replaces `bias`): encoder conv0's speaker term by edge class of the frame
     int act;
     void* out; int out_type; int ldo;
     float* out_t; const float* res_t;
@@ -172,6 +173,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int b = (mt / a.tiles_t) * a.BB + (r / a.TB);
             const bool valid = (t < a.gT) && (b < a.gB);
             const size_t m = (size_t)b * a.gT + t;
+            // bias row of this tile row: the layer's bias, or (row_bias) the utterance's vector for the frame's edge class - frames
+            // whose 5-tap window reaches into the zero padding lack the speaker term of the taps that fall outside
+            const float* brow = a.bias;
+            if (a.row_bias) {
+                const int cls = t == 0 ? 1 : (t == 1 ? 2 : (t == a.gT - 2 ? 3 : (t == a.gT - 1 ? 4 : 0)));
+                brow = a.row_bias + ((size_t)(b < a.gB ? b : a.gB - 1) * 5 + cls) * a.N;
+            }
             // channel-first addressing uses the true utterance length
             size_t ot_base = 0;
             if (a.out_t) { const size_t bb = m / a.T, tt = m - bb * a.T; ot_base = (bb * a.N) * a.T + tt; }
@@ -202,7 +210,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         const int n = n0 + c0 + sub;
 #pragma unroll
                         for (int j = 0; j < 16; j += 4) {
-                            const float4 bv = a.bias ? __ldg(reinterpret_cast<const float4*>(a.bias + n + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            const float4 bv = brow ? __ldg(reinterpret_cast<const float4*>(brow + n + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
                             v[j + 0] = __uint_as_float(rr[j + 0]) + bv.x;
                             v[j + 1] = __uint_as_float(rr[j + 1]) + bv.y;
                             v[j + 2] = __uint_as_float(rr[j + 2]) + bv.z;
@@ -271,7 +279,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int n = n0 + c0;
 #pragma unroll
                 for (int j = 0; j < 16; j += 4) {
-                    const float4 bv = a.bias ? __ldg(reinterpret_cast<const float4*>(a.bias + n + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float4 bv = brow ? __ldg(reinterpret_cast<const float4*>(brow + n + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
                     v[j + 0] = __uint_as_float(rr[j + 0]) + bv.x;
                     v[j + 1] = __uint_as_float(rr[j + 1]) + bv.y;
                     v[j + 2] = __uint_as_float(rr[j + 2]) + bv.z;
@@ -375,12 +383,13 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
         // plain GEMMs may have a ragged K tail: TMA zero-fills both operands beyond Kp
         if (p.taps != 1) return bad("conv Cp must be a multiple of 64");
     }
+    if (p.row_bias && (p.taps != KTAPS || p.T < 4)) return bad("row_bias is defined for 5-tap convolutions over utterances of at least 4 frames");
     TcGemmPlan* plan = new TcGemmPlan();
     TcGemmArgs& a = plan->args;
     a.N = p.N; a.taps = p.taps; a.Cp = p.Cp; a.pad = p.taps / 2;
     a.kblocks_per_tap = ceil_div(p.taps == 1 ? p.K : p.Cp, BLOCK_K);
     a.T = p.T;
-    a.bias = p.bias; a.act = p.act; a.out = p.out; a.out_type = p.out_type; a.ldo = p.ldo; a.out_t = p.out_t; a.res_t = p.res_t;
+    a.bias = p.bias; a.row_bias = p.row_bias; a.act = p.act; a.out = p.out; a.out_type = p.out_type; a.ldo = p.ldo; a.out_t = p.out_t; a.res_t = p.res_t;
 
     // ---- M tiling: tile = BB utterances x TB frames, TB*BB = 128 ----
     if (p.taps == 1) { a.gT = p.M; a.gB = 1; a.TB = BLOCK_M; a.BB = 1; }

@@ -321,3 +321,28 @@ def test_caller_device_is_restored():
     m(x, c_org, c_trg)
     probe = torch.empty(1, device="cuda")        # allocated on the CUDA runtime's current device
     assert torch.cuda.current_device() == 0 and probe.device.index == 0
+
+
+@pytest.mark.parametrize("B,T", [(3, 33), (2, 128), (5, 100), (1, 32)])
+def test_fused_speaker_concat_equals_materialised_concat(B, T, monkeypatch):
+    """Encoder conv0 with the speaker concat fused away (mel-only convolution + per-utterance edge-class bias vectors,
+    reference encoder.py:65-70) against the same layer over the materialised [B,T,336] operand (AVC_NO_FUSED_CONCAT=1):
+    the two differ only in where the fp32 partial sums are added, and both stay within the oracle tolerance - including
+    the first / last two frames of every utterance, whose windows reach into the zero padding."""
+    from oracle import autovc_oracle as O
+    m = model("bf16")
+    x, c_org, c_trg = synth_inputs(B, T, seed=700 + T)
+    fused = [t.clone() for t in m(x.cuda(), c_org.cuda(), c_trg.cuda())]
+    monkeypatch.setenv("AVC_NO_FUSED_CONCAT", "1")
+    plain = [t.clone() for t in m(x.cuda(), c_org.cuda(), c_trg.cuda())]
+    monkeypatch.delenv("AVC_NO_FUSED_CONCAT")
+    ref = O.generator_forward(synth_state_dict(0), x, c_org, c_trg)
+    d_codes = float((fused[2] - plain[2]).abs().max())
+    d_post = float((fused[1] - plain[1]).abs().max())
+    print(f"fused vs materialised B={B} T={T}: codes {d_codes:.2e} post {d_post:.2e}")
+    assert d_codes <= 2e-2 and d_post <= BF16_POST_TOL
+    for got in (fused, plain):
+        _check_rows("bf16", got, ref, f"concat B={B} T={T}")
+    # edge frames of the codes' source: the encoder output at t = 0 feeds the first backward code
+    n_f = T // 32
+    assert float((fused[2][:, 32 * n_f:32 * n_f + 32].cpu() - ref[2][:, 32 * n_f:32 * n_f + 32]).abs().max()) <= 2e-2

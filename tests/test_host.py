@@ -207,3 +207,15 @@ def test_staged_reference_matches_its_manifest():
         for rel, sha in files.items():
             with open(os.path.join(ref_loader.LIVE, rel), "rb") as f:
                 assert hashlib.sha256(f.read()).hexdigest() == sha, rel
+
+
+def test_conv0_split_for_fused_speaker_concat(host_engine):
+    """enc.conv0 split along the input channels (reference encoder.py:65-66 fused away): the mel part stays a 5-tap
+    convolution over 80 (padded to 128) channels, the speaker part becomes a [5*512][256] matrix (row tap*512 + n)."""
+    full = host_engine.packed("enc.conv0.w").view(512, 5, 384)
+    mel = host_engine.packed("enc.conv0.mel.w").view(512, 5, 128)
+    spk = host_engine.packed("enc.conv0.spk.w").view(5, 512, 256)
+    assert torch.equal(mel[:, :, :80], full[:, :, :80]) and float(mel[:, :, 80:].abs().max()) == 0.0
+    assert torch.equal(spk.permute(1, 0, 2), full[:, :, 80:336])
+    assert torch.equal(host_engine.packed("enc.conv0.mel.b"), host_engine.packed("enc.conv0.b"))
+    assert float(host_engine.packed("enc.conv0.spk.b").abs().max()) == 0.0
