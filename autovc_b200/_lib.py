@@ -22,7 +22,7 @@ AVC_PREC_FP32 = 1
 
 EXPORTS = ["avc_abi_version", "avc_create", "avc_load_weights", "avc_workspace_bytes", "avc_forward", "avc_encode", "avc_forward_bn_train",
            "avc_last_launch_count", "avc_plan_builds", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error",
-           "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_reduce",
+           "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_forward_static", "avc_se_reduce",
            "avc_mel_create", "avc_mel_num_frames", "avc_mel_filterbank", "avc_mel_forward", "avc_mel_last_error", "avc_mel_destroy",
            "avc_voc_create", "avc_voc_load_weights", "avc_voc_condition_workspace_bytes", "avc_voc_condition", "avc_voc_max_rows",
            "avc_voc_generate_workspace_bytes", "avc_voc_generate", "avc_voc_last_launch_count", "avc_voc_last_error", "avc_voc_destroy"]
@@ -88,6 +88,8 @@ def lib() -> ctypes.CDLL:
     L.avc_se_workspace_bytes.restype = c_size_t
     L.avc_se_forward.argtypes = [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]
     L.avc_se_forward.restype = c_int
+    L.avc_se_forward_static.argtypes = [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]
+    L.avc_se_forward_static.restype = c_int
     L.avc_se_reduce.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]
     L.avc_se_reduce.restype = c_int
     L.avc_mel_create.argtypes = [POINTER(c_void_p), POINTER(AvcMelConfig), c_int]

@@ -661,9 +661,21 @@ int run_se(avc_ctx* h, const float* partials, int N, int T, float* embeds, void*
 // ---------------------------------------------------------------------------------------------
 // extern "C"
 // ---------------------------------------------------------------------------------------------
+// ---------------------------------------------------------------------------------------------
+// allocation-free variant of avc_se_forward (no counterpart in the reference)
+// ---------------------------------------------------------------------------------------------
+// The scratch avc_se_forward takes from the caller lives here instead: one file-scope device array per GPU that loads the library
+// (held until the process exits).  In HOST code the name below is a host-side stand-in for the symbol, not a device address:
+// the address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_se_static_scratch[AVC_SE_STATIC_SCRATCH_BYTES];
+namespace {
+constexpr int MAX_DEVICES = 64;
+void* g_se_static_ptr[MAX_DEVICES] = {};      // per device: device address of g_se_static_scratch (nullptr: not resolved yet)
+}  // namespace
+
 extern "C" {
 
-int avc_abi_version(void) { return 6; }
+int avc_abi_version(void) { return 7; }
 
 int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision) {
     if (!out || !dims) return fail(nullptr, AVC_ERR_INVALID_ARG, "null out/dims");
@@ -909,6 +921,27 @@ size_t avc_se_workspace_bytes(avc_handle h, int N, int T) {
 int avc_se_forward(avc_handle h, const float* partials, int N, int T, float* embeds, void* workspace, size_t workspace_bytes,
                    void* stream) {
     return run_se(h, partials, N, T, embeds, workspace, workspace_bytes, stream);
+}
+
+int avc_se_forward_static(avc_handle h, const float* partials, int N, int T, float* embeds, void* stream) {
+    if (!h) return AVC_ERR_INVALID_ARG;
+    if (h->device < 0 || h->device >= MAX_DEVICES) return fail(h, AVC_ERR_INVALID_ARG, "avc_se_forward_static needs a context on device 0..%d", MAX_DEVICES - 1);
+    if (N <= 0 || T <= 0) return fail(h, AVC_ERR_INVALID_ARG, "non-positive N/T");
+    const size_t need = carve_se(h, nullptr, N, T).total;
+    if (need > (size_t)AVC_SE_STATIC_SCRATCH_BYTES)
+        return fail(h, AVC_ERR_WORKSPACE, "avc_se_forward_static: N=%d partials x T=%d frames need %zu bytes of scratch, the static array holds %zu "
+                    "(e.g. 8 x 160); use avc_se_forward with a caller workspace for larger batches", N, T, need, (size_t)AVC_SE_STATIC_SCRATCH_BYTES);
+    if (!g_se_static_ptr[h->device]) {         // set-up, once per device, with that device current
+        DeviceGuard guard;
+        cudaError_t e = guard.enter(h->device);
+        void* ptr = nullptr;
+        if (e == cudaSuccess) e = cudaGetSymbolAddress(&ptr, g_se_static_scratch);
+        if (e != cudaSuccess || !ptr) return fail(h, AVC_ERR_CUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", h->device, cudaGetErrorString(e));
+        g_se_static_ptr[h->device] = ptr;
+    }
+    // same schedule as avc_se_forward on the static array: no cudaMalloc / cudaFree anywhere below (plans are host objects; the
+    // recurrence re-arms its exchange region itself, every other buffer is fully overwritten, so stale contents are harmless)
+    return run_se(h, partials, N, T, embeds, g_se_static_ptr[h->device], (size_t)AVC_SE_STATIC_SCRATCH_BYTES, stream);
 }
 
 int avc_se_reduce(avc_handle h, const float* embeds, const int32_t* offsets, int S, float* speaker_embeds, void* stream) {

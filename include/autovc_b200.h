@@ -158,6 +158,20 @@ size_t avc_se_workspace_bytes(avc_handle h, int N, int T);
 int avc_se_forward(avc_handle h, const float* partials, int N, int T, float* embeds, void* workspace,
                    size_t workspace_bytes, void* stream);
 
+/* Allocation-free variant of avc_se_forward.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same computation and results as avc_se_forward, but the scratch is a file-scope static __device__ array of
+ * AVC_SE_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until the process exits) instead
+ * of a caller workspace; the call itself performs no cudaMalloc / cudaFree.  The caller still owns partials [N,T,40] and embeds
+ * [N,256] (device, float32).  Limit: avc_se_workspace_bytes(h, N, T) <= AVC_SE_STATIC_SCRATCH_BYTES - one utterance's 8 partial
+ * utterances of 160 frames (the reference's embed_utterance case) need 11.4 MiB; larger requests return AVC_ERR_WORKSPACE with a
+ * message naming the sizes.  All calls on a device share the one array: calls that overlap on the GPU (two streams, two
+ * threads, two handles on one device) race; run them one after another.  Nothing in the array has to be cleared between
+ * calls (the recurrence re-arms its exchange region at every launch, everything else is overwritten).  The first call on a
+ * device resolves the array's address (cudaGetSymbolAddress): make one call before starting a graph capture. */
+#define AVC_SE_STATIC_SCRATCH_BYTES (12u << 20)
+int avc_se_forward_static(avc_handle h, const float* partials, int N, int T, float* embeds, void* stream);
+
 /* embed_utterance's tail (model.py:185-186) for S speakers at once: speaker s = rows [offsets[s], offsets[s+1]) of
  * embeds; speaker_embeds[s] = mean of those rows, divided by its L2 norm.  offsets: DEVICE int32 [S+1]. */
 int avc_se_reduce(avc_handle h, const float* embeds, const int32_t* offsets, int S, float* speaker_embeds, void* stream);
@@ -245,7 +259,7 @@ void avc_voc_destroy(avc_voc_handle h);
 const char* avc_last_error(avc_handle h);
 
 /* ABI version; bumped on any signature change. */
-int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder; 5: avc_forward_bn_train; 6: avc_plan_builds (plan LRU) */
+int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder; 5: avc_forward_bn_train; 6: avc_plan_builds (plan LRU); 7: avc_se_forward_static */
 
 #ifdef __cplusplus
 }
