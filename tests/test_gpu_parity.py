@@ -346,3 +346,51 @@ def test_fused_speaker_concat_equals_materialised_concat(B, T, monkeypatch):
     # edge frames of the codes' source: the encoder output at t = 0 feeds the first backward code
     n_f = T // 32
     assert float((fused[2][:, 32 * n_f:32 * n_f + 32].cpu() - ref[2][:, 32 * n_f:32 * n_f + 32]).abs().max()) <= 2e-2
+
+
+@pytest.mark.parametrize("B,T,mode", [(3, 64, "forward"), (5, 100, "forward"), (2, 33, "encode"), (70, 40, "forward")])
+def test_workspace_and_outputs_stay_inside_their_bounds(B, T, mode):
+    """compute-sanitizer is closed on this GPU pool (profiles/r2_sanitizer.md), so out-of-bounds WRITES are hunted with guard
+    bands: the workspace and every output of avc_forward / avc_encode sit between 64 KiB bands of a known pattern inside
+    one allocation, called through the C ABI with exactly avc_workspace_bytes; afterwards every band must be untouched and
+    the results must equal those of the normal path."""
+    import ctypes
+    from autovc_b200 import _lib as L
+    m = model("bf16")
+    eng = m._engine(torch.device("cuda", 0))
+    x, c_org, c_trg = (t.cuda().contiguous() for t in synth_inputs(B, T, seed=900 + B))
+    want = m(x, c_org, c_trg) if mode == "forward" else (None, None, m(x, c_org, None))
+    G = 64 << 10
+    need = eng.workspace_bytes(B, T)
+    n_codes = 32 * (T // 32 + (T + 31) // 32)
+    sizes = [need, B * 80 * T * 4, B * 80 * T * 4, B * n_codes * 4]          # workspace, mel, mel_post, codes
+    offs, total = [], G
+    for sz in sizes:
+        offs.append(total)
+        total += (sz + 255) // 256 * 256 + G
+    arena = torch.full((total,), 0xA5, dtype=torch.uint8, device="cuda")
+    base = arena.data_ptr()
+    assert base % 256 == 0
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if mode == "forward":
+        rc = L.lib().avc_forward(eng._h, x.data_ptr(), c_org.data_ptr(), c_trg.data_ptr(), B, T, base + offs[1], base + offs[2],
+                                 base + offs[3], base + offs[0], need, stream)
+    else:
+        rc = L.lib().avc_encode(eng._h, x.data_ptr(), c_org.data_ptr(), B, T, base + offs[3], base + offs[0], need, stream)
+    assert rc == L.AVC_OK, L.last_error(eng._h)
+    torch.cuda.synchronize()
+    bands = [(0, G)] + [(o + (sz + 255) // 256 * 256, o + (sz + 255) // 256 * 256 + G) for o, sz in zip(offs, sizes)]
+    for lo, hi in bands:
+        assert bool((arena[lo:hi] == 0xA5).all()), f"guard band [{lo}, {hi}) was written"
+    # the slack between an output's end and its 256-byte rounding must be untouched too
+    for o, sz in zip(offs[1:], sizes[1:]):
+        end = o + (sz + 255) // 256 * 256
+        assert bool((arena[o + sz:end] == 0xA5).all())
+    codes = arena[offs[3]:offs[3] + sizes[3]].view(torch.float32).view(B, n_codes)
+    assert torch.equal(codes, want[2])
+    if mode == "forward":
+        post = arena[offs[2]:offs[2] + sizes[2]].view(torch.float32).view(B, 80, T)
+        mel = arena[offs[1]:offs[1] + sizes[1]].view(torch.float32).view(B, 80, T)
+        assert torch.equal(post, want[1]) and torch.equal(mel, want[0])
+    else:                                           # encode-only must not touch the mel outputs' slots at all
+        assert bool((arena[offs[1]:offs[1] + sizes[1]] == 0xA5).all()) and bool((arena[offs[2]:offs[2] + sizes[2]] == 0xA5).all())
