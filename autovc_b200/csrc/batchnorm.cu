@@ -64,7 +64,12 @@ __global__ void __launch_bounds__(BN_THREADS) bn_partial_kernel(const float* __r
 }
 
 // 32 channels per block, 32 warps split the chunks; the cross-warp sum runs in warp order
+// FUSED: the chunks come from the GEMM epilogue (tc_gemm.cu, STATS): four floats per (chunk, channel) - S1 = sum(x - shift),
+// S2 = sum((x - shift)^2), the chunk's own shift (its first valid row) and its number of valid rows - which are re-based here,
+// in double, onto the shift g of chunk 0:  d = shift - g,  S1' = S1 + n d,  S2' = S2 + 2 d S1 + n d^2.  Otherwise the chunks are
+// bn_partial's plain double-precision (sum, sum of squares).
 constexpr int FIN_WARPS = 32;
+template <bool FUSED>
 __global__ void __launch_bounds__(FIN_WARPS * 32) bn_finalize_kernel(const double* __restrict__ partial, int chunks, int M, int N,
                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                  float eps, float* __restrict__ scale_shift, float* __restrict__ stat_mean,
@@ -72,20 +77,31 @@ __global__ void __launch_bounds__(FIN_WARPS * 32) bn_finalize_kernel(const doubl
     __shared__ double sh[FIN_WARPS][2][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
-    double s = 0, q = 0;
-    if (c < N)
+    double s = 0, q = 0, g = 0;
+    if (c < N) {
+        if constexpr (FUSED) g = (double)reinterpret_cast<const float2*>(partial + N + c)->x;       // chunk 0 always has valid rows
 #pragma unroll 4
         for (int k = w; k < chunks; k += FIN_WARPS) {
-            s += partial[(size_t)k * 2 * N + c];
-            q += partial[(size_t)k * 2 * N + N + c];
+            if constexpr (FUSED) {
+                const float2 ss = *reinterpret_cast<const float2*>(partial + (size_t)k * 2 * N + c);
+                const float2 sn = *reinterpret_cast<const float2*>(partial + (size_t)k * 2 * N + N + c);
+                const double d = (double)sn.x - g, n = (double)sn.y;
+                s += (double)ss.x + n * d;
+                q += (double)ss.y + 2.0 * d * (double)ss.x + n * d * d;
+            } else {
+                s += partial[(size_t)k * 2 * N + c];
+                q += partial[(size_t)k * 2 * N + N + c];
+            }
         }
+    }
     sh[w][0][lane] = s; sh[w][1][lane] = q;
     __syncthreads();
     if (w == 0 && c < N) {
         double S = 0, Q = 0;
         for (int k = 0; k < FIN_WARPS; ++k) { S += sh[k][0][lane]; Q += sh[k][1][lane]; }
-        const double mean = S / M;
-        double var = Q / M - mean * mean;
+        const double mean_g = S / M;                      // mean relative to g (g = 0 for the plain sums)
+        const double mean = g + mean_g;
+        double var = Q / M - mean_g * mean_g;
         if (var < 0) var = 0;
         const double sc = (double)gamma[c] / sqrt(var + (double)eps);
         scale_shift[c] = (float)sc;
@@ -165,7 +181,8 @@ cudaError_t launch_bn_train(const BnTrainParams& p, cudaStream_t s, int* launche
         const int rpp = BN_THREADS / (p.N / 4);
         bn_partial_kernel<<<chunks, BN_THREADS, (size_t)rpp * 2 * p.N * sizeof(double), s>>>(p.Z, p.partial, p.M, p.N, rows_per_chunk);
     }
-    bn_finalize_kernel<<<ceil_div(p.N, 32), FIN_WARPS * 32, 0, s>>>(p.partial, chunks, p.M, p.N, p.gamma, p.beta, p.eps, p.scale_shift, p.stat_mean, p.stat_var);
+    if (fused_chunks > 0) bn_finalize_kernel<true><<<ceil_div(p.N, 32), FIN_WARPS * 32, 0, s>>>(p.partial, chunks, p.M, p.N, p.gamma, p.beta, p.eps, p.scale_shift, p.stat_mean, p.stat_var);
+    else bn_finalize_kernel<false><<<ceil_div(p.N, 32), FIN_WARPS * 32, 0, s>>>(p.partial, chunks, p.M, p.N, p.gamma, p.beta, p.eps, p.scale_shift, p.stat_mean, p.stat_var);
     if (p.out_t) {
         dim3 grid(ceil_div(p.T, 32), p.M / p.T);
         bn_apply_t_kernel<<<grid, BN_THREADS, (size_t)32 * (p.N + 1) * sizeof(float), s>>>(p.Z, p.scale_shift, p.out_t, p.res_t, p.T, p.N);

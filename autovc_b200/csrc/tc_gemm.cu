@@ -254,19 +254,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         ptx::bulk_commit_group();
                     }
                     if constexpr (STATS) {
-                        // lane = column of the staged 32 x 32 fp32 block (swizzled 16-byte pieces: conflict-free), rows in order
+                        // lane = column of the staged 32 x 32 fp32 block (swizzled 16-byte pieces: conflict-free), rows in order.
+                        // SHIFTED sums: the block's first valid row is subtracted before summing, so the fp32 sums carry the
+                        // column's spread, not its offset (E[x^2] - mean^2 over raw fp32 sums loses the variance of a channel whose
+                        // |mean| >> std).  Chunk record = 4 floats in the two 8-byte slots: (S1, S2), (shift, valid rows);
+                        // bn_finalize re-bases every chunk onto one shift in double precision.
                         const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
                         const uint32_t col = ptx::smem_u32(stg) + buf + (uint32_t)((lane & 3) * 4);
+                        auto at_row = [&](int rr2) {
+                            float x;
+                            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(col + (uint32_t)(rr2 * 128) + ((((uint32_t)lane >> 2) ^ (uint32_t)(rr2 & 7)) << 4)));
+                            return x;
+                        };
+                        const float shift = vmask ? at_row(__ffs(vmask) - 1) : 0.0f;
                         float ssum = 0.0f, ssq = 0.0f;
 #pragma unroll
                         for (int rr2 = 0; rr2 < 32; ++rr2) {
-                            float x;
-                            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(col + (uint32_t)(rr2 * 128) + ((((uint32_t)lane >> 2) ^ (uint32_t)(rr2 & 7)) << 4)));
+                            const float x = at_row(rr2) - shift;
                             if ((vmask >> rr2) & 1u) { ssum += x; ssq = fmaf(x, x, ssq); }
                         }
                         double* pp = a.stat_partial + ((size_t)(mt * 4 + q) * 2) * a.N + (n0 + c0 + lane);
-                        pp[0] = (double)ssum;
-                        pp[a.N] = (double)ssq;
+                        *reinterpret_cast<float2*>(pp) = make_float2(ssum, ssq);
+                        *reinterpret_cast<float2*>(pp + a.N) = make_float2(shift, (float)__popc(vmask));
                     }
                 }
             } else

@@ -100,3 +100,50 @@ def test_training_shape_batch_statistics_against_oracle_properties():
     assert float((mean - beta).abs().max()) <= 1e-4
     assert float((var / gamma ** 2 - 1).abs().max()) <= 1e-3
     assert m.last_launch_count >= 24 + 2 * 11     # per BatchNorm layer at least finalize + apply on top of the GEMM (statistics fused or not)
+
+
+def test_fused_statistics_survive_a_large_channel_offset(monkeypatch):
+    """A channel whose |mean| >> std (conv bias +300 on encoder conv0's channel 7, +1000 on decoder conv1's channel 100): the
+    statistics fused into the GEMM epilogue (fp32 sums of each 32-row block, shifted by the block's first row) must give
+    the variance the separate double-precision statistics pass gives - unshifted fp32 sums lose it to cancellation
+    (E[x^2] - mean^2 with x^2 ~ 1e5..1e6).  B x T = 8192 rows so that the fused kernels (256/128-wide tiles) are taken."""
+    sd = synth_state_dict(0)
+    sd["encoder.convolutions.0.0.conv.bias"] = sd["encoder.convolutions.0.0.conv.bias"].clone()
+    sd["encoder.convolutions.0.0.conv.bias"][7] += 300.0
+    sd["decoder.convolutions.1.0.conv.bias"] = sd["decoder.convolutions.1.0.conv.bias"].clone()
+    sd["decoder.convolutions.1.0.conv.bias"][100] += 1000.0
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(64, 128, seed=12))
+    import autovc_b200
+
+    def stats(no_fused):
+        if no_fused:
+            monkeypatch.setenv("AVC_BN_NO_FUSED_STATS", "1")
+        else:
+            monkeypatch.delenv("AVC_BN_NO_FUSED_STATS", raising=False)
+        m = autovc_b200.AutoEncoder(device="cuda", verbose=False, precision="bf16", batch_stat_bn=True)     # own context: own plan cache
+        m.load_state_dict(sd)
+        m.train()
+        eng = m._engine(torch.device("cuda", 0), params_only=True)
+        out = torch.ops.autovc_b200.generator_forward_bn_train(x, c_org, c_trg, eng.id)
+        torch.cuda.synchronize()
+        return out[3].cpu().double(), eng.last_launch_count
+
+    fused, n_fused = stats(False)
+    plain, n_plain = stats(True)
+    monkeypatch.delenv("AVC_BN_NO_FUSED_STATS", raising=False)
+    assert n_fused < n_plain                                   # the fused run really skipped statistics passes
+    # Layers 0-2 see bit-identical inputs in both runs: the two statistics paths must agree to fp32 rounding, offset channel included
+    # (its variance is 0.03 under a mean of 300: unshifted fp32 sums were off by ~25 % there).  From layer 3 on the runs differ
+    # legitimately (1e-6 differences in upstream statistics flip bf16 roundings, the recurrences in between amplify them to ~1e-3),
+    # so the +1000 channel of layer 4 is held to 5e-3 - the cancellation error it guards against was ~8 %.
+    for layer, ch, off, tol in ((0, 7, 300.0, 1e-5), (4, 100, 1000.0, 5e-3)):
+        mf, vf, mp, vp = fused[layer, 0, ch], fused[layer, 1, ch], plain[layer, 0, ch], plain[layer, 1, ch]
+        print(f"layer {layer} ch {ch}: mean {float(mf):.4f} / {float(mp):.4f}, var {float(vf):.6f} / {float(vp):.6f}")
+        assert abs(float(mp)) > 0.9 * off and float(vp) > 1e-3
+        assert abs(float(mf - mp)) <= 1e-4 * abs(float(mp))
+        assert abs(float(vf - vp)) <= tol * float(vp)
+    for layer in (0, 1, 2):
+        assert float(((fused[layer, 1, :512] - plain[layer, 1, :512]).abs() / plain[layer, 1, :512]).max()) <= 1e-5
+        assert float((fused[layer, 0, :512] - plain[layer, 0, :512]).abs().max()) <= 1e-5
+    for layer, n in ((4, 512), (10, 80)):
+        assert float(((fused[layer, 1, :n] - plain[layer, 1, :n]).abs() / plain[layer, 1, :n]).max()) <= 1e-2
