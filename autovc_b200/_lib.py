@@ -21,7 +21,7 @@ AVC_PREC_BF16 = 0
 AVC_PREC_FP32 = 1
 
 EXPORTS = ["avc_abi_version", "avc_create", "avc_load_weights", "avc_workspace_bytes", "avc_forward", "avc_encode", "avc_forward_bn_train",
-           "avc_last_launch_count", "avc_plan_builds", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error",
+           "avc_last_launch_count", "avc_plan_builds", "avc_graph_replays", "avc_set_profiling", "avc_get_profile", "avc_debug_packed", "avc_debug_gemm", "avc_destroy", "avc_last_error",
            "avc_se_load_weights", "avc_se_workspace_bytes", "avc_se_forward", "avc_se_forward_static", "avc_se_reduce",
            "avc_mel_create", "avc_mel_num_frames", "avc_mel_filterbank", "avc_mel_forward", "avc_mel_last_error", "avc_mel_destroy",
            "avc_voc_create", "avc_voc_load_weights", "avc_voc_condition_workspace_bytes", "avc_voc_condition", "avc_voc_max_rows",
@@ -73,6 +73,8 @@ def lib() -> ctypes.CDLL:
     L.avc_last_launch_count.restype = c_int64
     L.avc_plan_builds.argtypes = [c_void_p]
     L.avc_plan_builds.restype = c_int64
+    L.avc_graph_replays.argtypes = [c_void_p]
+    L.avc_graph_replays.restype = c_int64
     L.avc_set_profiling.argtypes = [c_void_p, c_int]
     L.avc_set_profiling.restype = c_int
     L.avc_get_profile.argtypes = [c_void_p, POINTER(c_float), c_int]

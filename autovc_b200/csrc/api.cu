@@ -85,11 +85,26 @@ struct PlanSet {
     uint64_t stamp = 0;
     std::vector<TcGemmPlan*> plans;
     std::vector<LlLstmPlan*> llplans;
+    // CUDA graphs of this plan set's whole launch sequence, keyed on the caller's pointers (see run()): at most GRAPHS_PER_SET,
+    // least recently used first out
+    struct GraphEntry {
+        const void* key[7] = {};       // x, c_org, c_trg, mel, mel_post, codes, bn_stats
+        cudaGraphExec_t exec = nullptr;
+        int seen = 0;                  // calls with this key so far (the graph is built on the second)
+        bool failed = false;           // capture or instantiation failed once: this key keeps the plain launch sequence
+        int64_t launches = 0;
+        uint64_t stamp = 0;
+    };
+    std::vector<GraphEntry> graphs;
+    int captures = 0;              // graphs built for this plan set ...
+    int64_t replays = 0;           // ... and launches they served: building is rationed by their ratio (see run())
     ~PlanSet() {
         for (auto* p : plans) tc_gemm_plan_destroy(p);
         for (auto* p : llplans) ll_lstm_plan_destroy(p);
+        for (auto& g : graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
     }
 };
+constexpr size_t GRAPHS_PER_SET = 6;
 constexpr size_t PLAN_CACHE_ENTRIES = 8;
 
 // restores the caller's current device when an entry point returns (the library switches to the context's device)
@@ -125,6 +140,9 @@ struct avc_ctx {
     std::vector<PlanSet*> plan_cache;
     uint64_t plan_clock = 0;
     int64_t plan_builds = 0;
+    int64_t graph_replays = 0;   // forwards that ran as one cudaGraphLaunch
+    bool no_graph = false;       // AVC_NO_GRAPH=1 / AVC_LSTM_TRACE: always the plain launch sequence
+    cudaStream_t capture_stream = nullptr;   // private stream the graphs are captured on
     bool simt_lstm = false;    // AVC_SIMT_LSTM=1: debugging aid, per-step CUDA-core recurrences in the bf16 mode
     // optional per-phase timing (avc_set_profiling): events at phase boundaries of the last run
     bool profiling = false;
@@ -526,6 +544,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         r.ps = plan_set_for(h, workspace, B, T, mode, &r.building_plans);
     }
 
+    auto enqueue = [&]() {
     const int at = act_type(h), pt = post_type(h);
     const int M = B * T;
     const int dn = d.dim_neck, E = d.dim_emb, P = d.dim_pre;
@@ -591,6 +610,80 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         r.conv_bn(10, w.actB, pt, CONV_CH, M, T, ACT_NONE, nullptr, DT_F32, 0, mel_post, mel);
     }
     r.mark(AVC_PHASE_COUNT);  // closing marker
+    };   // enqueue
+
+    // ---- one CUDA graph per (plan set, caller pointers) ----
+    // The forward is ~27 launches.  Enqueued one by one they cost the stream ~60 us of launch boundaries per step and - measured,
+    // profiles/r2_e2e_scaling.md - every boundary stalls further while another stream (the host pipeline's copies) has work in
+    // flight: a 21 MB device->host copy beside the step cost 0.18 ms.  Replayed as ONE graph the step is 2.28 ms instead of 2.34
+    // and indifferent to concurrent copies.  So: the second call that repeats a call's pointers (steady-state loops do - a
+    // pipeline's slots, or torch's allocator handing the same blocks back) captures the sequence (thread-local capture mode, on a
+    // private stream), instantiates it and launches it on the caller's stream; later calls just launch it.  Not while plans are being built,
+    // not under the caller's own capture, not with per-phase profiling or the step trace on.  AVC_NO_GRAPH=1 turns it off.
+    PlanSet::GraphEntry* ge = nullptr;
+    if (r.ps && !r.building_plans && !h->profiling && !h->no_graph) {
+        cudaStreamCaptureStatus cst = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(r.s, &cst) == cudaSuccess && cst == cudaStreamCaptureStatusNone) {
+            const void* key[7] = {x, c_org, c_trg, mel, mel_post, codes, bn_stats};
+            for (auto& g : r.ps->graphs)
+                if (!memcmp(g.key, key, sizeof key)) { ge = &g; break; }
+            if (!ge) {
+                if (r.ps->graphs.size() >= GRAPHS_PER_SET) {
+                    size_t lru = 0;
+                    for (size_t i = 1; i < r.ps->graphs.size(); ++i)
+                        if (r.ps->graphs[i].stamp < r.ps->graphs[lru].stamp) lru = i;
+                    if (r.ps->graphs[lru].exec) cudaGraphExecDestroy(r.ps->graphs[lru].exec);
+                    r.ps->graphs.erase(r.ps->graphs.begin() + lru);
+                }
+                r.ps->graphs.emplace_back();
+                ge = &r.ps->graphs.back();
+                memcpy(ge->key, key, sizeof key);
+            }
+            ge->stamp = ++h->plan_clock;
+            ge->seen++;
+        }
+    }
+    if (ge && ge->exec) {
+        e = cudaGraphLaunch(ge->exec, r.s);
+        if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaGraphLaunch: %s", cudaGetErrorString(e));
+        h->launches = ge->launches;
+        h->graph_replays++; r.ps->replays++;
+        return AVC_OK;
+    }
+    // Building a graph costs a few milliseconds.  A caller whose pointers never settle (more live pointer sets than the cache
+    // holds, results kept alive so that every call gets new blocks) would pay it again and again for graphs that are evicted
+    // before they are reused: builds are rationed - three up front, then one more per eight replays the set's graphs have served.
+    if (ge && ge->seen >= 2 && !ge->failed && r.ps->captures < 3 + r.ps->replays / 8) {
+        r.ps->captures++;
+        // captured on a private stream of the context (the caller's may be the legacy default stream, which cannot capture; and
+        // its state is none of our business), launched on the caller's
+        cudaGraph_t graph = nullptr;
+        const cudaStream_t user_stream = r.s;
+        e = h->capture_stream ? cudaSuccess : cudaStreamCreateWithFlags(&h->capture_stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamBeginCapture(h->capture_stream, cudaStreamCaptureModeThreadLocal);
+        if (e == cudaSuccess) {
+            r.s = h->capture_stream;
+            enqueue();
+            r.s = user_stream;
+            e = cudaStreamEndCapture(h->capture_stream, &graph);   // always ends the capture, also after a failed launch inside it
+            if (e == cudaSuccess && r.ok() && graph) e = cudaGraphInstantiate(&ge->exec, graph, 0);
+            else if (e == cudaSuccess) e = cudaErrorUnknown;
+            if (graph) cudaGraphDestroy(graph);
+        }
+        if (e == cudaSuccess && ge->exec) {
+            ge->launches = h->launches;
+            e = cudaGraphLaunch(ge->exec, r.s);
+            if (e != cudaSuccess) return fail(h, AVC_ERR_CUDA, "cudaGraphLaunch: %s", cudaGetErrorString(e));
+            h->graph_replays++; r.ps->replays++;
+            return AVC_OK;
+        }
+        // capture failed: nothing ran.  Forget the error, remember not to try again, and fall through to the plain sequence.
+        (void)cudaGetLastError();
+        ge->failed = true; ge->exec = nullptr;
+        r.rc = AVC_OK; h->err.clear(); h->launches = 0;
+        r.plan_cursor = r.llplan_cursor = 0; r.cur_cat = -1;
+    }
+    enqueue();
     if (!r.ok() && r.building_plans && r.ps) drop_plan_set(h, r.ps);   // do not keep a half-built plan set
     return r.rc;
 }
@@ -675,7 +768,7 @@ void* g_se_static_ptr[MAX_DEVICES] = {};      // per device: device address of g
 
 extern "C" {
 
-int avc_abi_version(void) { return 7; }
+int avc_abi_version(void) { return 8; }
 
 int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision) {
     if (!out || !dims) return fail(nullptr, AVC_ERR_INVALID_ARG, "null out/dims");
@@ -695,6 +788,7 @@ int avc_create(avc_handle* out, const avc_dims* dims, int device, int precision)
     const char* sl = getenv("AVC_SIMT_LSTM");
     h->simt_lstm = sl && sl[0] == '1';
     h->gx_f32 = getenv("AVC_GX_F32") != nullptr;
+    h->no_graph = getenv("AVC_NO_GRAPH") != nullptr || getenv("AVC_LSTM_TRACE") != nullptr;
     for (int i = 0; i < L_COUNT; ++i) h->layers[i].name = kLayerNames[i];
     if (device >= 0) {
         DeviceGuard guard;
@@ -818,6 +912,8 @@ int avc_forward_bn_train(avc_handle h, const float* x, const float* c_org, const
 int64_t avc_last_launch_count(avc_handle h) { return h ? h->launches : 0; }
 
 int64_t avc_plan_builds(avc_handle h) { return h ? h->plan_builds : 0; }
+
+int64_t avc_graph_replays(avc_handle h) { return h ? h->graph_replays : 0; }
 
 int avc_set_profiling(avc_handle h, int enable) {
     if (!h) return AVC_ERR_INVALID_ARG;
@@ -968,6 +1064,7 @@ void avc_destroy(avc_handle h) {
             if (h->bn_beta_dev[i]) cudaFree(h->bn_beta_dev[i]);
         }
         drop_plans(h);
+        if (h->capture_stream) cudaStreamDestroy(h->capture_stream);
         for (auto ev : h->prof_events) cudaEventDestroy(ev);
     }
     delete h;

@@ -190,6 +190,10 @@ class Engine:
     def plan_builds(self) -> int:
         return int(L.lib().avc_plan_builds(self._h))
 
+    @property
+    def graph_replays(self) -> int:
+        return int(L.lib().avc_graph_replays(self._h))
+
     def close(self) -> None:
         if self._h:
             L.lib().avc_destroy(self._h)

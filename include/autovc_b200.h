@@ -112,6 +112,15 @@ int64_t avc_last_launch_count(avc_handle h);
  * between B=256 steps, the training pair's encode-only pass - do not rebuild them (tests, diagnostics). */
 int64_t avc_plan_builds(avc_handle h);
 
+/* avc_forward / avc_encode / avc_forward_bn_train replay their whole launch sequence as ONE CUDA graph once a call repeats an
+ * earlier call's pointers (x, c_org, c_trg, outputs) on the same workspace / B / T: the second such call captures the
+ * sequence (thread-local capture mode, on a private stream of the context) and launches the instantiated graph on the caller's
+ * stream, later ones only launch it (up to 6 pointer sets per shape, least recently used first out).  Results are identical; the step is shorter and no
+ * longer slowed by copies in flight on other streams.  Calls made while the caller itself is capturing, with profiling on,
+ * or with AVC_NO_GRAPH=1 in the environment take the plain sequence.  Returns the number of forwards that ran as a graph
+ * launch since avc_create (tests, diagnostics). */
+int64_t avc_graph_replays(avc_handle h);
+
 /* Optional per-phase device timing of the NEXT runs: CUDA events are recorded on the caller's stream at phase
  * boundaries; avc_get_profile() synchronises on the last one and returns the milliseconds spent per phase in the
  * most recent run (ms must have room for AVC_PHASE_COUNT floats).  bench.py uses this for the roofline object. */
@@ -259,7 +268,7 @@ void avc_voc_destroy(avc_voc_handle h);
 const char* avc_last_error(avc_handle h);
 
 /* ABI version; bumped on any signature change. */
-int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder; 5: avc_forward_bn_train; 6: avc_plan_builds (plan LRU); 7: avc_se_forward_static */
+int avc_abi_version(void);   /* 2: speaker-encoder entry points; 3: mel front-end; 4: vocoder; 5: avc_forward_bn_train; 6: avc_plan_builds (plan LRU); 7: avc_se_forward_static; 8: avc_graph_replays (graph replay of repeated calls) */
 
 #ifdef __cplusplus
 }

@@ -394,3 +394,69 @@ def test_workspace_and_outputs_stay_inside_their_bounds(B, T, mode):
         assert torch.equal(post, want[1]) and torch.equal(mel, want[0])
     else:                                           # encode-only must not touch the mel outputs' slots at all
         assert bool((arena[offs[1]:offs[1] + sizes[1]] == 0xA5).all()) and bool((arena[offs[2]:offs[2] + sizes[2]] == 0xA5).all())
+
+
+def test_repeated_calls_replay_one_cuda_graph(monkeypatch):
+    """A call that repeats an earlier call's pointers runs as ONE graph launch (built on the second such call) with results
+    bitwise equal to the plain launch sequence (AVC_NO_GRAPH=1); a different pointer set gets its own graph; profiling mode
+    and a reloaded state dict fall back to / rebuild the plain sequence."""
+    import autovc_b200
+    sd = synth_state_dict(0)
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(5, 100, seed=31))
+    monkeypatch.setenv("AVC_NO_GRAPH", "1")
+    plain_m = autovc_b200.AutoEncoder(device="cuda", verbose=False, precision="bf16")
+    plain_m.load_state_dict(sd)
+    want = [t.clone() for t in plain_m(x, c_org, c_trg)]
+    want_codes = plain_m(x, c_org, None).clone()
+    assert plain_m._engine(x.device).graph_replays == 0
+    monkeypatch.delenv("AVC_NO_GRAPH")
+    m = autovc_b200.AutoEncoder(device="cuda", verbose=False, precision="bf16")
+    m.load_state_dict(sd)
+    eng = m._engine(x.device)
+    out_a = tuple(torch.empty_like(t) for t in want)
+    out_b = tuple(torch.empty_like(t) for t in want)
+    for i in range(5):
+        for out in (out_a, out_b):
+            for t in out:
+                t.fill_(float("nan"))
+            m(x, c_org, c_trg, out=out)
+            assert all(torch.equal(a, b) for a, b in zip(out, want)), f"call {i}"
+    # out_a: call 0 builds the plans, call 1 is the first sighting of its pointers, calls 2-4 run as a graph (3);
+    # out_b: call 0 is the first sighting, calls 1-4 run as a graph (4)
+    assert eng.graph_replays == 7
+    n = eng.graph_replays
+    for _ in range(4):                                    # fresh output tensors: torch's allocator hands the same blocks back
+        assert torch.equal(m(x, c_org, None), want_codes)
+    assert eng.graph_replays > n
+    n, launches = eng.graph_replays, eng.last_launch_count
+    assert launches >= 6
+    eng.set_profiling(True)
+    m(x, c_org, c_trg, out=out_a)
+    assert eng.graph_replays == n and sum(eng.profile().values()) > 0
+    eng.set_profiling(False)
+    m.load_state_dict(sd)                                 # weights re-packed: plans and graphs are rebuilt, results unchanged
+    for _ in range(3):
+        m(x, c_org, c_trg, out=out_a)
+    assert all(torch.equal(a, b) for a, b in zip(out_a, want))
+
+
+def test_forward_inside_a_callers_own_graph_capture():
+    """When the caller is capturing (torch.cuda.graph) the library must not start a capture of its own: the plain sequence is
+    recorded into the caller's graph, and replaying that graph reproduces the eager result."""
+    m = model("bf16")
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(3, 64, seed=41))
+    want = [t.clone() for t in m(x, c_org, c_trg)]
+    out = tuple(torch.empty_like(t) for t in want)
+    for _ in range(3):
+        m(x, c_org, c_trg, out=out)                        # the library's own graph for this pointer set exists by now
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            m(x, c_org, c_trg, out=out)
+    for t in out:
+        t.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    assert all(torch.equal(a, b) for a, b in zip(out, want))

@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     lib = ctypes.CDLL(built_lib)
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/autovc_b200.h but not exported"
-    assert lib.avc_abi_version() == 7
+    assert lib.avc_abi_version() == 8
 
 
 def test_state_dict_contract():
