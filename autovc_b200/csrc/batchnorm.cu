@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(FIN_WARPS * 32) bn_finalize_kernel(const doubl
 }
 
 __device__ __forceinline__ float bn_act(float v, int act) {
-    if (act == ACT_RELU) return fmaxf(v, 0.0f);
+    if (act == ACT_RELU) return v < 0.0f ? 0.0f : v;          // like torch.relu: a NaN stays a NaN (fmaxf would return 0)
     if (act == ACT_TANH) return tanhf(v);
     return v;
 }

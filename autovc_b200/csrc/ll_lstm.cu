@@ -36,12 +36,19 @@
 //                    Issue loops are ROLLED over the K chunks with running descriptor words: ptxas then keeps the sequence on
 //                    the uniform datapath; unrolled, it builds every descriptor in vector registers and pays ~2 R2UR per MMA.
 //
-// Exchange protocol ("the data is the flag"): CTAs exchange h through an L2-resident buffer Yx laid out as
-// [T][32-utterance tile][H/8 planes][32 rows][8 bf16], pre-filled with the bit pattern 0xFFFF (a NaN that the float->bf16
-// conversion never produces: it canonicalises NaN to 0x7FFF).  Producers store h_t as 32-bit words (two units of one
-// utterance, both from one thread); consumers read with strong (L1-bypassing) coalesced 16-byte loads, treat any 32-bit word
-// of all ones as "not written yet" (32-bit accesses are single-copy atomic) and fetch the missing pieces again, together.  No
-// step counter, no release/acquire fence pair, no second round trip between "flag seen" and "data fetched".
+// Exchange protocol ("the data is the flag"): CTAs exchange h through an L2-resident RING of two step slots,
+// Yx[2][32-utterance tile][H/8 planes][32 rows][8 bf16] (1 MiB at B = 256, H = 1024).  |h| <= 1 (h = o tanh(c)), so bit 14 of a
+// bf16 h - the top exponent bit, set only for |x| >= 2, Inf and NaN - is always 0 and carries a one-bit EPOCH instead: step t
+// writes slot t & 1 with epoch (t >> 1) & 1.  A slot's previous content (step t-2) has the opposite epoch, the pre-fill (0xFF,
+// once per launch, 1 MiB) reads as epoch 1 for the epoch-0 steps 0 and 1: "not written yet" is "wrong epoch in any 32-bit word"
+// (32-bit accesses are single-copy atomic and both halves of a word come from one thread).  Producers store h_t as tagged
+// 32-bit words; consumers read with strong (L1-bypassing) coalesced 16-byte loads, fetch the missing pieces again, together,
+// and strip the tag on the way into the operand tile.  No step counter, no release/acquire fence pair, no second round trip
+// between "flag seen" and "data fetched", and no T-sized buffer to pre-fill and write back (67 MB per lstm2 layer before).
+// Two slots suffice: a CTA that stores h_t has consumed h_{t-1} from every producer of its tile, so every one of them had finished
+// step t-1 and therefore had read all of h_{t-2} - the content the store replaces; and no CTA can be two steps ahead of a reader.
+// A non-finite h (NaN / Inf in the inputs) would carry bit 14 itself: the exchange copy then gets +-1 in its place (the
+// recurrence stays alive) while the output copy Y keeps the true value, so the NaN still reaches the results.
 // No acc_empty barrier either: a sub-tile's operands for step t+1 are published by the very warps that read its accumulators of
 // step t, so "operands complete" implies "accumulators drained" in both CTAs.
 //
@@ -67,7 +74,7 @@ constexpr int KBLK = 64;                  // K elements per chunk (128 bytes per
 constexpr int W_BLK_BYTES = MROWS * KBLK * 2;     // 16 KiB (shared-memory part of W)
 constexpr int PLANE_ELEMS = 8;            // Yx plane width: 8 bf16 = 16 B
 constexpr uint32_t TMEM_COLS = 512;
-constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
+constexpr uint32_t EPOCH_BITS = 0x40004000u;          // bit 14 of both bf16 halves of a 32-bit word: the step epoch of the exchange ring
 constexpr int SUB_N = 32;                 // utterances per (sub-)tile = UMMA N
 constexpr int SUB_ROWS = SUB_N / 2;       // rows of h staged per CTA and sub-tile
 constexpr int GROUP_WARPS = 8;            // loader + epilogue warps per sub-tile
@@ -84,7 +91,7 @@ struct LlLstmArgs {
     const void* Gx;              // [B][Tg][4H] fp32 (or fp16: GXH kernels), unit-major gate order, bias included
     const __nv_bfloat16* Whh;    // [4H][H] bf16, unit-major gate rows (sigmoid rows pre-scaled by 0.5, api.cu::pack_lstm)
     __nv_bfloat16* Y;            // [B][T][H] bf16 output sequence for the next layer
-    __nv_bfloat16* Yx;           // exchange copy: [T][tiles][H/8][32][8] bf16, pre-filled with 0xFF
+    __nv_bfloat16* Yx;           // exchange ring: [2][tiles][H/8][32][8] bf16 (epoch-tagged), pre-filled with 0xFF
     int tiles, tile0;            // 32-utterance tiles in Yx, first tile of this launch
     long long y_sb, y_st;        // element strides of Y along utterance / frame
     long long gx_sb, gx_st;      // same for Gx rows (frame index t / gx_div)
@@ -101,8 +108,8 @@ __device__ __forceinline__ uint4 ld_strong(const void* p) {
     asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ bool unwritten(const uint4& v) {
-    return v.x == SENTINEL || v.y == SENTINEL || v.z == SENTINEL || v.w == SENTINEL;
+__device__ __forceinline__ bool unwritten(const uint4& v, uint32_t etag) {      // etag: EPOCH_BITS or 0, the epoch the piece must carry
+    return (((v.x ^ etag) | (v.y ^ etag) | (v.z ^ etag) | (v.w ^ etag)) & EPOCH_BITS) != 0u;
 }
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
@@ -343,7 +350,8 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             gx_smem = gx_smem0 + (uint32_t)((t & 1) * GXB);
             if (t >= 1) {
                 // ---- h_{t-1} of this sub-tile: L2 -> registers (poll) -> swizzled operand tile ----
-                const size_t soff = (size_t)(t - 1) * step_elems;
+                const size_t soff = (size_t)((t - 1) & 1) * step_elems;                       // ring slot of h_{t-1} ...
+                const uint32_t etag = (((uint32_t)(t - 1) >> 1) & 1u) * EPOCH_BITS;           // ... and its epoch
                 if (tg == 0) AVC_TRACE2(g, 0);
                 uint4 v[NP];
 #pragma unroll
@@ -352,7 +360,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     bool missing = false;
 #pragma unroll
                     for (int i = 0; i < NP; ++i)
-                        if (unwritten(v[i])) { v[i] = ld_strong(piece_src(i) + soff); missing = true; }
+                        if (unwritten(v[i], etag)) { v[i] = ld_strong(piece_src(i) + soff); missing = true; }
                     if (!missing) break;
                     if (spin > (1u << 22)) {
                         printf("autovc_b200: lstm h poll timed out (slice %d tile %d sub %d t %d warp %d lane %d)\n", ns, bt, g, t, wg, lane);
@@ -363,6 +371,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 #pragma unroll
                 for (int i = 0; i < NP; ++i) {
                     const int pl = piece_plane(i);
+                    v[i].x &= ~EPOCH_BITS; v[i].y &= ~EPOCH_BITS; v[i].z &= ~EPOCH_BITS; v[i].w &= ~EPOCH_BITS;      // strip the epoch
                     st_shared_v4(sH_g + (uint32_t)(piece_chunk(i) * HBLK2 + lrow * 128 + ((pl ^ (lrow & 7)) << 4)), v[i]);
                 }
                 ptx::fence_proxy_async_smem();
@@ -442,7 +451,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             // h_t out, straight from registers.  The lane holds one unit x four utterances (hp[0] = columns 0,1; hp[1] = columns 2,3
             // of its block); lanes j and j ^ 4 hold neighbouring units of the same utterances.  One exchange gives every lane a
             // (unit pair) x (two utterances) block, i.e. two 32-bit words: the validity protocol needs whole 32-bit words from one
-            // thread (a word with one stale half would not read as "unwritten").  No shared-memory staging, no barrier.
+            // thread (a word with one stale half must not pass the epoch check).  No shared-memory staging, no barrier.
             {
                 const bool odd = (lane >> 2) & 1;
                 const uint32_t mine = odd ? hp[1] : hp[0];
@@ -451,10 +460,20 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 const uint32_t w0 = __byte_perm(ev, od, 0x5410), w1 = __byte_perm(ev, od, 0x7632);
                 const int col = half * CPT2 + gj * H2 + (odd ? 2 : 0);                  // first of the two utterances (within the sub-tile)
                 const int upair = (lane >> 3) * 2;                                       // even unit of the pair, within this quarter's 8
-                __nv_bfloat16* yx = yx_tile + (size_t)t * step_elems + ((size_t)(ns * 4 + q) * SUB_N + col) * PLANE_ELEMS + upair;
+                __nv_bfloat16* yx = yx_tile + (size_t)(t & 1) * step_elems + ((size_t)(ns * 4 + q) * SUB_N + col) * PLANE_ELEMS + upair;
                 if (t + 1 < a.T) {
-                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx), "r"(w0) : "memory");
-                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx + PLANE_ELEMS), "r"(w1) : "memory");
+                    uint32_t x0 = w0, x1 = w1;
+                    if ((x0 | x1) & EPOCH_BITS) {      // non-finite h (never for finite inputs): +-1 in the exchange copy, see the header
+                        auto fix = [](uint32_t w) {
+                            if (w & 0x00004000u) w = (w & 0xffff8000u) | 0x00003f80u;
+                            if (w & 0x40000000u) w = (w & 0x8000ffffu) | 0x3f800000u;
+                            return w;
+                        };
+                        x0 = fix(x0); x1 = fix(x1);
+                    }
+                    const uint32_t ptag = (((uint32_t)t >> 1) & 1u) * EPOCH_BITS;
+                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx), "r"(x0 | ptag) : "memory");
+                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx + PLANE_ELEMS), "r"(x1 | ptag) : "memory");
                 }
                 __nv_bfloat16* y = a.Y + (size_t)t * a.y_st + (size_t)ns * SLICE_UNITS + q * 8 + upair;
                 if (b0 + col < a.B) *reinterpret_cast<uint32_t*>(y + (size_t)(b0 + col) * a.y_sb) = w0;
@@ -503,7 +522,7 @@ struct LlLstmPlan {
     int nsub;                 // 32-utterance sub-tiles per CTA pair: 1 or 2
     bool gx_f16;
     int smem_bytes;
-    void* yx_base; size_t yx_bytes;       // region to pre-fill with the "unwritten" pattern before every launch
+    void* yx_base; size_t yx_bytes;       // the exchange ring, pre-filled with 0xFF before every launch
 };
 
 const char* ll_lstm_init() {
@@ -523,7 +542,7 @@ const char* ll_lstm_init() {
     return nullptr;
 }
 
-size_t ll_lstm_exchange_bytes(int B, int T, int H) { return (size_t)T * ceil_div(B, 2 * SUB_N) * 2 * SUB_N * H * 2; }
+size_t ll_lstm_exchange_bytes(int B, int T, int H) { (void)T; return (size_t)2 * ceil_div(B, 2 * SUB_N) * 2 * SUB_N * H * 2; }   // the two-slot ring
 
 LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_type, int Tg, int gx_div, void* Y, void* Yx, int B, int T, int H,
                                 int num_sms, const char** err) {
@@ -545,7 +564,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
     plan->nsub = nsub;
     plan->smem_bytes = smem_for(nkb, plan->gx_f16, nsub);
     const int tnp = SUB_N * nsub;                                    // utterances per CTA pair
-    plan->yx_base = Yx; plan->yx_bytes = (size_t)T * ceil_div(B, tnp) * tnp * H * 2;
+    plan->yx_base = Yx; plan->yx_bytes = (size_t)2 * ceil_div(B, tnp) * tnp * H * 2;       // two step slots
     {
         cuuint64_t gdim[2] = {(cuuint64_t)H, (cuuint64_t)4 * H};
         cuuint64_t gstr[1] = {(cuuint64_t)H * 2};
@@ -582,7 +601,7 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
     static long long* d_trace = nullptr;
     const bool tracing = getenv("AVC_LSTM_TRACE") != nullptr;
     if (tracing && !d_trace) cudaMalloc(&d_trace, sizeof(long long) * TRACE_WORDS);
-    // "unwritten" pattern: every 16-bit element = 0xFFFF
+    // the ring starts as "epoch 1 everywhere" (0xFF...), which the epoch-0 steps 0 and 1 read as not written yet
     cudaError_t e = cudaMemsetAsync(plan->yx_base, 0xFF, plan->yx_bytes, s);
     if (e != cudaSuccess) return e;
     for (size_t i = 0; i < plan->args.size(); ++i) {

@@ -46,7 +46,7 @@ __device__ __forceinline__ void store1(__half* p, float v) { *p = __float2half_r
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 __device__ __forceinline__ float apply_act(float v, int act) {
-    if (act == ACT_RELU) return fmaxf(v, 0.0f);
+    if (act == ACT_RELU) return v < 0.0f ? 0.0f : v;          // like torch.relu: a NaN stays a NaN (fmaxf would return 0)
     if (act == ACT_TANH) return tanhf(v);
     return v;
 }

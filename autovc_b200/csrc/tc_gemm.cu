@@ -218,7 +218,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         }
                         if (a.act == ACT_RELU) {
 #pragma unroll
-                            for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.0f);
+                            for (int j = 0; j < 16; ++j) v[j] = v[j] < 0.0f ? 0.0f : v[j];     // like torch.relu: a NaN stays a NaN (fmaxf would return 0)
                         } else if (a.act == ACT_TANH) {
 #pragma unroll
                             for (int j = 0; j < 16; ++j) v[j] = fast_tanh(v[j]);
@@ -296,7 +296,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 if (a.act == ACT_RELU) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.0f);
+                    for (int j = 0; j < 16; ++j) v[j] = v[j] < 0.0f ? 0.0f : v[j];     // like torch.relu: a NaN stays a NaN (fmaxf would return 0)
                 } else if (a.act == ACT_TANH) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] = fast_tanh(v[j]);

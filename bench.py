@@ -411,6 +411,14 @@ def main():
     x1, co1, ct1 = x[:1].contiguous(), c_org[:1].contiguous(), c_trg[:1].contiguous()
     lat_p50 = p50(lambda: model(x1, co1, ct1), 3, 50)
 
+    # per-rank record (N > 1): every rank's own step time and SM clock under load, gathered outside the timed regions
+    per_rank = None
+    if dist is not None:
+        mine = torch.tensor([dev_ms / K, e2e_ms / K, float(clocks.get("sm_mhz") or 0.0)], dtype=torch.float64, device=dev)
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"ms_per_step": [round(float(t[0]), 4) for t in allr], "e2e_ms_per_step": [round(float(t[1]), 4) for t in allr],
+                    "sm_mhz": [float(t[2]) for t in allr]}
     dev_ms, e2e_ms = max_over_ranks(dev_ms, e2e_ms)
 
     # ---- the other BASELINE.json configs, same process, a few steps each (device events, max over ranks) ----
@@ -528,7 +536,8 @@ def main():
             "config": {"workload": f"config2: B={B} x T={T} x 80 mel per GPU, dims 32/256/512/32, seeded random-init weights",
                        "l2": "256 MB flush written between timed iterations (excluded from the timing)",
                        "parallelism": f"replicas x{world}, no data-path collective",
-                       "e2e": "HostPipeline: pinned host buffers, per-step H2D and D2H on two copy streams overlapped with the previous/next step's compute"},
+                       "e2e": "HostPipeline: pinned host buffers, per-step H2D and D2H on two copy streams overlapped with the previous/next step's compute",
+                       "launch": "the forward's 27 kernel launches are replayed as one CUDA graph built by the library on the second call with the same pointers"},
             "realtime_x": value / REALTIME_FRAMES_PER_S,
             "whole_path_tensor_frac": value / world * FLOP_PER_FRAME / (peak * 1e12),
             "whole_path_tensor_frac_burst": value / world * FLOP_PER_FRAME / (burst * 1e12),
@@ -543,6 +552,8 @@ def main():
                          "algorithmic_flop_per_launch_group": dom_flops},
             "wall_s_timed_region": wall,
         }
+        if per_rank:
+            line["per_rank"] = per_rank
         if configs:
             line["configs"] = configs
         if world == 1 and not args.no_configs:

@@ -460,3 +460,21 @@ def test_forward_inside_a_callers_own_graph_capture():
     g.replay()
     torch.cuda.synchronize()
     assert all(torch.equal(a, b) for a, b in zip(out, want))
+
+
+def test_nan_input_reaches_the_outputs_without_stalling_the_exchange():
+    """The recurrence's exchange ring uses bit 14 of every bf16 h as its epoch tag (|h| <= 1 keeps it free); a NaN h would carry
+    that bit itself.  A NaN frame in one utterance must neither stall / trap the poll loops nor touch the other utterances, and
+    must still show up as NaN in that utterance's outputs (the untagged output copy keeps it)."""
+    m = model("bf16")
+    x, c_org, c_trg = (t.cuda() for t in synth_inputs(3, 96, seed=51))
+    clean = [t.clone() for t in m(x, c_org, c_trg)]
+    xn = x.clone()
+    xn[1, :, 40] = float("nan")
+    mel, post, codes = m(xn, c_org, c_trg)
+    torch.cuda.synchronize()
+    assert torch.isnan(post[1]).any() and torch.isnan(mel[1]).any()
+    for r in (0, 2):
+        assert torch.equal(post[r], clean[1][r]) and torch.equal(codes[r], clean[2][r])
+    again = m(x, c_org, c_trg)                         # and the context is still healthy
+    assert all(torch.equal(a, b) for a, b in zip(again, clean))
