@@ -171,6 +171,8 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     const size_t tile_elems = (size_t)a.H * SUB_N;                      // one (t, 32-row tile) block of Yx
     const size_t step_elems = tile_elems * a.tiles;
 
+#define AVC_TRACE_PRO(pt) do { if (a.trace && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) a.trace[2 * TRACE_STEPS * TR_PTS + (pt)] = clock64(); } while (0)
+    AVC_TRACE_PRO(0);
     if (warp == 0) {
         if (lane == 0) {
             if (NKB_S > 0) ptx::prefetch_tmap(&tmW);
@@ -190,6 +192,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     if (*tmem_slot != 0u) { if (threadIdx.x == 0) printf("autovc_b200: unexpected TMEM base %u\n", *tmem_slot); __trap(); }
     constexpr uint32_t tmem_base = 0u;
     constexpr uint32_t W_COL = D_COLS2;
+    AVC_TRACE_PRO(1);
 
     // ---- resident W: tensor-memory slot s holds chunk (s / HT) * NKB/2 + HS + s % HT, shared-memory slot j chunk (j / HS) * NKB/2 + j % HS ----
     if (warp < 4) {
@@ -211,10 +214,12 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             ptx::tma_load_2d(sW + j * W_BLK_BYTES, &tmW, wfull, ((j / (HS > 0 ? HS : 1)) * (NKB / 2) + j % (HS > 0 ? HS : 1)) * KBLK, ns * MROWS);
         ptx::mbar_wait(wfull, 0);
     }
+    AVC_TRACE_PRO(2);
     ptx::tc_fence_before();
     __syncthreads();
     ptx::cluster_sync();
     ptx::tc_fence_after();
+    AVC_TRACE_PRO(3);
 
     if (warp >= ISSUE_WARP) {
         // ===================== MMA issuers (leader CTA): K half ih of A(t), B(t), A(t+1), ... =====================
@@ -623,6 +628,9 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
                     "landed published | quarters ready q0..q3 (issuers), committed | Gx wait entered, Gx ready | acc_seen tmem_read gates cell stored | "
                     "publish time of warps 0..7 || absolute start\n", args.H, args.B, plan->grids[i].x, plan->grids[i].y, plan->nsub);
             const long long t00 = hbuf[0];
+            { const long long* pr = hbuf + 2 * TRACE_STEPS * TR_PTS;
+              fprintf(stderr, "  prologue (cycles since kernel entry, thread 0 of CTA (0,0)): barriers+TMEM alloc %lld, W resident (own warp) %lld, cluster synced %lld; first traced step starts at %lld\n",
+                      pr[1] - pr[0], pr[2] - pr[0], pr[3] - pr[0], t00 - pr[0]); }
             for (int st = 0; st < TRACE_STEPS; ++st)
                 for (int g = 0; g < plan->nsub; ++g) {
                     const long long* r = hbuf + (st * 2 + g) * TR_PTS;
