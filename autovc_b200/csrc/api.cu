@@ -556,8 +556,7 @@ int run(avc_ctx* h, const float* x, const float* c_org, const float* c_trg, int 
         // Fused speaker concat (reference encoder.py:65-66): cat(x, c_org expanded over t) is never built.  conv0 runs over the 80 mel
         // channels only (K = 5 x 128 instead of 5 x 384); the speaker channels' share - constant in t but for the frames whose window
         // reaches into the zero padding - is one [B, E] x [E, 5 x 512] GEMM and enters conv0's epilogue as a per-utterance bias.
-        r.check(launch_pack_input(x, c_org, w.X0, at, B, T, 0, r.s), "pack_input (mel)"); h->launches++;
-        r.check(launch_cast_pad_rows(c_org, w.Cb, at, B, E, E, r.s), "cast c_org"); h->launches++;
+        r.check(launch_pack_mel(x, c_org, w.X0, w.Cb, B, T, E, r.s), "pack mel + c_org"); h->launches++;
         r.gemm(L_ENC_CONV0_SPK, w.Cb, at, E, B, 1, ACT_NONE, w.Sspk, DT_F32, KTAPS * CONV_CH);
         r.mark(AVC_PHASE_LAYOUT);
         r.check(launch_speaker_edge(w.Sspk, h->layers[L_ENC_CONV0_MEL].b_dev, w.Espk, B, CONV_CH, r.s), "speaker edge vectors"); h->launches++;

@@ -52,6 +52,8 @@ cudaError_t launch_simt_gemm(const GemmParams& p, cudaStream_t s);
 cudaError_t launch_simt_lstm_step(const LstmStepParams& q, int ndir, cudaStream_t s);
 cudaError_t launch_pack_input(const float* x, const float* c_org, void* X0, int out_type, int B, int T, int E,
                               cudaStream_t s);
+// fused-concat path: x (B,80,T) fp32 -> X0 [B][T][80] bf16 and c_org [B][E] fp32 -> Cb bf16, one launch (E even)
+cudaError_t launch_pack_mel(const float* x, const float* c_org, void* X0_bf16, void* Cb_bf16, int B, int T, int E, cudaStream_t s);
 // encoder conv0 speaker term: S [B][5][N] (per-tap products) + bias [N] -> E [B][5][N] (bias vectors per edge class)
 cudaError_t launch_speaker_edge(const float* S, const float* bias, float* E, int B, int N, cudaStream_t s);
 cudaError_t launch_codes(const float* Y, const float* c_trg, float* codes, void* D, int d_type, int B, int T, int dn,

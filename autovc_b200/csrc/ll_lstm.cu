@@ -163,6 +163,8 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     uint64_t* acc_full = bars + 1;                             // [2] the MMAs (both K halves) of a sub-tile's step are complete
     uint64_t* gfull = bars + 4;                                // [2][4] chunk quarter q of sub-tile g is in shared memory (both CTAs)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    uint64_t* wst_full = bars + 16;                            // [2] prologue: a 16 KiB chunk of W_hh has landed in staging buffer i
+    uint64_t* wst_empty = bars + 18;                           // [2] ... and has been moved on to tensor memory
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int ns = blockIdx.x;            // unit slice (32 units)
@@ -175,11 +177,12 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     AVC_TRACE_PRO(0);
     if (warp == 0) {
         if (lane == 0) {
-            if (NKB_S > 0) ptx::prefetch_tmap(&tmW);
+            ptx::prefetch_tmap(&tmW);
             ptx::mbar_init(wfull, 1);
             for (int i = 0; i < 8; ++i) ptx::mbar_init(&gfull[i], 2 * (GROUP_WARPS / 4));   // 2 loader warps per quarter in each CTA
             ptx::mbar_init(&acc_full[0], 2);                                                 // one commit per issuing warp
             ptx::mbar_init(&acc_full[1], 2);
+            for (int i = 0; i < 2; ++i) { ptx::mbar_init(&wst_full[i], 1); ptx::mbar_init(&wst_empty[i], 4); }
             ptx::fence_barrier_init();
         }
         __syncwarp();
@@ -195,24 +198,40 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     AVC_TRACE_PRO(1);
 
     // ---- resident W: tensor-memory slot s holds chunk (s / HT) * NKB/2 + HS + s % HT, shared-memory slot j chunk (j / HS) * NKB/2 + j % HS ----
-    if (warp < 4) {
-        const int R = warp * 32 + lane;
-        const __nv_bfloat16* wrow = a.Whh + (size_t)(ns * MROWS + R) * a.H;
-        const uint32_t wl = tmem_base + W_COL + ((uint32_t)(warp * 32) << 16);
-        for (int sl = 0; sl < NKB_T; ++sl) {
-            const int kc = (sl / HT) * (NKB / 2) + HS + sl % HT;
-            uint4 v[8];
+    // Tensor-memory chunks travel global -> (TMA, 16 KiB swizzled boxes, two staging buffers in the not yet used operand-tile /
+    // Gx area) -> registers (thread = gate row: eight conflict-free 16-byte reads) -> tcgen05.st.  One row per thread straight
+    // from global memory (16 bytes per lane at a 2 KiB stride, a dependent round per chunk) took 7 of the launch's 19 fixed us.
+    {
+        uint8_t* wstage = sH;                                  // 2 x 16 KiB; sH .. end of the Gx / transpose areas is >= 56 KiB in every instantiation
+        if (warp < 4) {
+            const int R = warp * 32 + lane;
+            const uint32_t wl = tmem_base + W_COL + ((uint32_t)(warp * 32) << 16);
+            for (int sl = 0; sl < NKB_T; ++sl) {
+                const int st = sl & 1;
+                ptx::mbar_wait(&wst_full[st], (uint32_t)(sl >> 1) & 1);
+                const uint32_t row = ptx::smem_u32(wstage) + (uint32_t)(st * W_BLK_BYTES + R * 128);
+                uint4 v[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = __ldg(reinterpret_cast<const uint4*>(wrow + kc * KBLK) + i);
-            ptx::tmem_st32(wl + (uint32_t)(sl * 32), reinterpret_cast<const uint32_t(&)[32]>(v));
+                for (int i = 0; i < 8; ++i) v[i] = ld_shared_v4(row + (uint32_t)((i ^ (R & 7)) << 4));
+                ptx::tmem_st32(wl + (uint32_t)(sl * 32), reinterpret_cast<const uint32_t(&)[32]>(v));
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&wst_empty[st]);       // the reads above have returned (the store consumed them)
+            }
+            ptx::tmem_st_wait();
+        } else if (warp == 4 && lane == 0) {
+            if (NKB_S > 0) {                                   // the shared-memory-resident chunks first: they need no staging buffer
+                ptx::mbar_expect_tx(wfull, (uint32_t)(NKB_S * W_BLK_BYTES));
+                for (int j = 0; j < NKB_S; ++j)
+                    ptx::tma_load_2d(sW + j * W_BLK_BYTES, &tmW, wfull, ((j / (HS > 0 ? HS : 1)) * (NKB / 2) + j % (HS > 0 ? HS : 1)) * KBLK, ns * MROWS);
+            }
+            for (int sl = 0; sl < NKB_T; ++sl) {
+                const int st = sl & 1, kc = (sl / HT) * (NKB / 2) + HS + sl % HT;
+                if (sl >= 2) ptx::mbar_wait(&wst_empty[st], (uint32_t)((sl >> 1) - 1) & 1);
+                ptx::mbar_expect_tx(&wst_full[st], (uint32_t)W_BLK_BYTES);
+                ptx::tma_load_2d(wstage + st * W_BLK_BYTES, &tmW, &wst_full[st], kc * KBLK, ns * MROWS);
+            }
+            if (NKB_S > 0) ptx::mbar_wait(wfull, 0);
         }
-        ptx::tmem_st_wait();
-    }
-    if (NKB_S > 0 && warp == 4 && lane == 0) {
-        ptx::mbar_expect_tx(wfull, (uint32_t)(NKB_S * W_BLK_BYTES));
-        for (int j = 0; j < NKB_S; ++j)
-            ptx::tma_load_2d(sW + j * W_BLK_BYTES, &tmW, wfull, ((j / (HS > 0 ? HS : 1)) * (NKB / 2) + j % (HS > 0 ? HS : 1)) * KBLK, ns * MROWS);
-        ptx::mbar_wait(wfull, 0);
     }
     AVC_TRACE_PRO(2);
     ptx::tc_fence_before();

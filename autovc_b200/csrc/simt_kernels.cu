@@ -324,12 +324,45 @@ __global__ void speaker_edge_kernel(const float* __restrict__ S, const float* __
     e[4 * N] = bb + (s0 + s1 + s2);
 }
 
+// Encoder input for the fused-concat path: the 80 mel channels of x (B,80,T) fp32 channel-first -> X0 [B][T][80] bf16 channel-last
+// (one 16-byte store of 8 channels per thread; the loads of a warp run along t), and - same launch, the blocks behind the mel part -
+// c_org [B][E] fp32 -> bf16 for the speaker-term GEMM.  Replaces pack_input_kernel (32x32 shared-memory transposes, 11 us for 5 MB)
+// + cast_pad_rows on that path.  reference encoder.py:65-66 (what is left of the concat)
+__global__ void __launch_bounds__(256) pack_mel_kernel(const float* __restrict__ x, const float* __restrict__ c_org, __nv_bfloat16* __restrict__ X0,
+                                                       __nv_bfloat16* __restrict__ Cb, int B, int T, int E, int mel_blocks) {
+    if ((int)blockIdx.x < mel_blocks) {
+        const long long i = (long long)blockIdx.x * 256 + threadIdx.x;          // (b, channel group of 8, t), t fastest
+        const long long per_b = (long long)(N_MELS / 8) * T;
+        if (i >= per_b * B) return;
+        const int b = (int)(i / per_b), r = (int)(i - (long long)b * per_b), cg = r / T, t = r - cg * T;
+        const float* src = x + ((size_t)b * N_MELS + cg * 8) * T + t;
+        uint32_t pk[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(src[(size_t)(2 * j) * T], src[(size_t)(2 * j + 1) * T]);
+            pk[j] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        *reinterpret_cast<uint4*>(X0 + ((size_t)b * T + t) * N_MELS + cg * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    } else {
+        const long long i = ((long long)(blockIdx.x - mel_blocks) * 256 + threadIdx.x) * 2;
+        if (i >= (long long)B * E) return;
+        *reinterpret_cast<__nv_bfloat162*>(Cb + i) = __floats2bfloat162_rn(c_org[i], c_org[i + 1]);
+    }
+}
+
 cudaError_t launch_pack_input(const float* x, const float* c_org, void* X0, int out_type, int B, int T, int E,
                               cudaStream_t s) {
     dim3 grid(ceil_div(T, 32), 1, B), block(32, 8);
     if (out_type == DT_F32) pack_input_kernel<float><<<grid, block, 0, s>>>(x, c_org, (float*)X0, B, T, E);
     else if (out_type == DT_BF16) pack_input_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(x, c_org, (__nv_bfloat16*)X0, B, T, E);
     else pack_input_kernel<__half><<<grid, block, 0, s>>>(x, c_org, (__half*)X0, B, T, E);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_mel(const float* x, const float* c_org, void* X0_bf16, void* Cb_bf16, int B, int T, int E, cudaStream_t s) {
+    const long long n_mel = (long long)B * (N_MELS / 8) * T, n_c = ((long long)B * E + 1) / 2;
+    const int mel_blocks = (int)((n_mel + 255) / 256), c_blocks = (int)((n_c + 255) / 256);
+    pack_mel_kernel<<<mel_blocks + c_blocks, 256, 0, s>>>(x, c_org, (__nv_bfloat16*)X0_bf16, (__nv_bfloat16*)Cb_bf16, B, T, E, mel_blocks);
     return cudaGetLastError();
 }
 
