@@ -478,3 +478,22 @@ def test_nan_input_reaches_the_outputs_without_stalling_the_exchange():
         assert torch.equal(post[r], clean[1][r]) and torch.equal(codes[r], clean[2][r])
     again = m(x, c_org, c_trg)                         # and the context is still healthy
     assert all(torch.equal(a, b) for a, b in zip(again, clean))
+
+
+@pytest.mark.parametrize("B,T", [(7, 57), (33, 45), (2, 257), (17, 96), (1, 129), (40, 32), (129, 64), (65, 33)])
+def test_ragged_shapes_match_oracle(B, T):
+    """Ragged (B, T) pairs - partial 32-utterance tiles, one and two sub-tiles per CTA pair (B = 129 crosses the switch), T not a
+    multiple of 32 or of the GEMM tile, T = freq - in bf16 against the oracle on up to four sampled rows, and in fp32 on two."""
+    from oracle import autovc_oracle as O
+    sd = synth_state_dict(0)
+    x, c_org, c_trg = synth_inputs(B, T, seed=1000 + 7 * B + T)
+    rows = sorted({0, B // 3, (2 * B) // 3, B - 1})
+    idx = torch.tensor(rows)
+    ref = O.generator_forward(sd, x[idx], c_org[idx], c_trg[idx])
+    mel, post, codes = model("bf16")(x.cuda(), c_org.cuda(), c_trg.cuda())
+    assert codes.shape == (B, 32 * (T // 32 + (T + 31) // 32))
+    _check_rows("bf16", (mel[idx.cuda()], post[idx.cuda()], codes[idx.cuda()]), ref, f"ragged B={B} T={T}")
+    assert torch.isfinite(post).all()
+    two = idx[:2]
+    mel32, post32, codes32 = model("fp32")(x[two].cuda(), c_org[two].cuda(), c_trg[two].cuda())
+    _check_rows("fp32", (mel32, post32, codes32), tuple(r[:2] for r in ref), f"ragged fp32 B={B} T={T}")
