@@ -20,7 +20,7 @@ out = [f"# ncu --set full summaries, round 2, capture {tag} (B200, config 2: B=2
        f"bench line of the same build and box: `r2_bench_{tag}.json`.\n"]
 traffic = {}
 for f, title in [('lstm_raw.csv', 'll_lstm_kernel (lstm1 H=512, then the two lstm2 layers H=1024)'),
-                 ('gemm_raw.csv', 'tc_gemm_kernel (the 20 launches of one forward, in order)')]:
+                 ('gemm_raw.csv', 'tc_gemm_kernel (the 18 launches of one forward, in order)')]:
     rows = list(csv.reader(open(os.path.join(go, f)))); hdr, units = rows[0], rows[1]
     out.append(f"## {title}\n")
     out.append("| metric | unit | " + " | ".join(str(i + 1) for i in range(len(rows) - 2)) + " |")
