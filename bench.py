@@ -537,7 +537,7 @@ def main():
                        "l2": "256 MB flush written between timed iterations (excluded from the timing)",
                        "parallelism": f"replicas x{world}, no data-path collective",
                        "e2e": "HostPipeline: pinned host buffers, per-step H2D and D2H on two copy streams overlapped with the previous/next step's compute",
-                       "launch": "the forward's 27 kernel launches are replayed as one CUDA graph built by the library on the second call with the same pointers"},
+                       "launch": "the forward's kernel launches (26 at config 2) are replayed as one CUDA graph built by the library on the second call with the same pointers"},
             "realtime_x": value / REALTIME_FRAMES_PER_S,
             "whole_path_tensor_frac": value / world * FLOP_PER_FRAME / (peak * 1e12),
             "whole_path_tensor_frac_burst": value / world * FLOP_PER_FRAME / (burst * 1e12),
