@@ -26,7 +26,7 @@
 //
 // Warp roles (NSUB x 8 + 2 warps):
 //   warps 8g..8g+7   sub-tile g: loaders of its h_{t-1} rows (poll -> swizzled K-major operand tile -> fence.proxy.async ->
-//                    arrive on the chunk quarter's mbarrier of the leader CTA) AND its gate epilogue (tcgen05.ld of 16 columns per
+//                    arrive on the mbarrier of its own K part in the leader CTA) AND its gate epilogue (tcgen05.ld of 16 columns per
 //                    thread, + Gx_t, MUFU.TANH gates, cell update with c in registers, h_t stores)
 //   last two warps   MMA issuers (leader CTA), one K half each into its own accumulator, each strictly alternating
 //                    A(t), B(t), A(t+1), ... in program order.  That order (a) keeps the accumulation order independent of timing
@@ -144,7 +144,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     constexpr int NKB_T = NKB < MAX_TMEM_CHUNKS2 ? NKB : MAX_TMEM_CHUNKS2;
     constexpr int NKB_S = NKB - NKB_T;
     // WHICH chunks live in shared memory: the first HS of each K half (chunks 0.., NKB/2..), i.e. the start of each issuer's first
-    // quarter.  MMAs with A in shared memory take 40 cycles against 17: issued first, they run while the later quarters are still
+    // part.  MMAs with A in shared memory take 40 cycles against 17: issued first, they run while the later parts are still
     // arriving; kept at the end of K (the one-tile kernel's choice) they would be the 650-cycle tail behind the last arrival.
     constexpr int HS = NKB_S / 2, HT = NKB / 2 - HS;          // per K half: chunks in shared memory / in tensor memory
     static_assert(NKB_S % 2 == 0 && HS <= NKB / 4, "smem-resident chunks must fit the first quarter of each K half");
@@ -161,10 +161,17 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     uint64_t* bars = reinterpret_cast<uint64_t*>(sGT + NSUB * GT_BYTES);
     uint64_t* wfull = bars;                                    // [1]
     uint64_t* acc_full = bars + 1;                             // [2] the MMAs (both K halves) of a sub-tile's step are complete
-    uint64_t* gfull = bars + 4;                                // [2][4] chunk quarter q of sub-tile g is in shared memory (both CTAs)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
-    uint64_t* wst_full = bars + 16;                            // [2] prologue: a 16 KiB chunk of W_hh has landed in staging buffer i
-    uint64_t* wst_empty = bars + 18;                           // [2] ... and has been moved on to tensor memory
+    uint64_t* gfull = bars + 4;                                // [2][PARTS] part p of sub-tile g's K chunks is in shared memory (both CTAs)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+    uint64_t* wst_full = bars + 22;                            // [2] prologue: a 16 KiB chunk of W_hh has landed in staging buffer i
+    uint64_t* wst_empty = bars + 24;                           // [2] ... and has been moved on to tensor memory
+    // K is handed to the issuers in PARTS pieces.  One sub-tile: eight, each the chunks ONE loader warp of either CTA fills - the
+    // MMAs left to issue when the last piece of h_{t-1} lands are an eighth of the step's (same-box A/B: config 3 9.75 -> 9.57 ms,
+    // B = 1 p50 1.18 -> 1.16 ms).  Two sub-tiles (and H = 256): quarters - there the issuers share their schedulers with the other
+    // sub-tile's epilogue, and twice the barrier waits cost more issue slots than the shorter tail returns (lstm2 0.875 -> 0.90 ms).
+    constexpr int PARTS = (NSUB == 1 && NKB >= GROUP_WARPS) ? GROUP_WARPS : 4;
+    constexpr int WPP = GROUP_WARPS / PARTS;                           // loader warps per part in each CTA
+    constexpr int CPP = NKB / PARTS;                                   // chunks per part: 4, 2 or 1
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int ns = blockIdx.x;            // unit slice (32 units)
@@ -179,7 +186,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         if (lane == 0) {
             ptx::prefetch_tmap(&tmW);
             ptx::mbar_init(wfull, 1);
-            for (int i = 0; i < 8; ++i) ptx::mbar_init(&gfull[i], 2 * (GROUP_WARPS / 4));   // 2 loader warps per quarter in each CTA
+            for (int i = 0; i < 2 * PARTS; ++i) ptx::mbar_init(&gfull[i], 2 * WPP);          // the part's loader warps of both CTAs
             ptx::mbar_init(&acc_full[0], 2);                                                 // one commit per issuing warp
             ptx::mbar_init(&acc_full[1], 2);
             for (int i = 0; i < 2; ++i) { ptx::mbar_init(&wst_full[i], 1); ptx::mbar_init(&wst_empty[i], 4); }
@@ -255,19 +262,20 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                         // sequence on the uniform datapath (UIADD3 / UMOV between the UTCHMMAs); unrolled, it computes every
                         // descriptor in vector registers and pays ~2 R2UR per MMA - 27 cycles per MMA from one warp, against
                         // the 17 the pipe needs at N = 32 (tools/micro/mma_burst.cu, profiles/r2_ll_lstm_notes.md).
-                        auto issue_quarter = [&](auto Q) {
-                            constexpr int q = decltype(Q)::value;
-                            constexpr int c0 = q * (NKB / 4), c1 = c0 + NKB / 4;
-                            constexpr int ss_end = (q & 1) == 0 ? c0 + HS : c0;           // [c0, ss_end) A in smem (first quarter of a K half), [ss_end, c1) A in TMEM
-                            ptx::mbar_wait(&gfull[g * 4 + q], par);
+                        auto issue_part = [&](auto P) {
+                            constexpr int p = decltype(P)::value;
+                            constexpr int c0 = p * CPP, c1 = c0 + CPP;
+                            constexpr int ss_lim = ih * (NKB / 2) + HS;                   // end of this K half's smem-resident chunks
+                            constexpr int ss_end = ss_lim < c0 ? c0 : (ss_lim > c1 ? c1 : ss_lim);   // [c0, ss_end) A in smem, [ss_end, c1) A in TMEM
+                            ptx::mbar_wait(&gfull[g * PARTS + p], par);
                             ptx::tc_fence_after();
-                            if (q == 0 && ih == 0 && lane == 0) AVC_TRACE2(g, 8);
-                            if (lane == 0) AVC_TRACE2(g, 10 + q);
+                            if (p == 0 && lane == 0) AVC_TRACE2(g, 8);
+                            if (p % (PARTS / 4) == 0 && lane == 0) AVC_TRACE2(g, 10 + p / (PARTS / 4));
                             const uint64_t bd0 = ptx::umma_desc_sw128(sH_u + (uint32_t)((g * NKB + c0) * HBLK2));
                             const uint32_t b_hi = (uint32_t)(bd0 >> 32);
                             uint32_t b_lo = (uint32_t)bd0;
                             if constexpr (c0 < ss_end) {
-                                const uint64_t ad0 = ptx::umma_desc_sw128(sW_u + (uint32_t)(ih * HS * W_BLK_BYTES));
+                                const uint64_t ad0 = ptx::umma_desc_sw128(sW_u + (uint32_t)((ih * HS + c0 - ih * (NKB / 2)) * W_BLK_BYTES));
                                 const uint32_t a_hi = (uint32_t)(ad0 >> 32);
                                 uint32_t a_lo = (uint32_t)ad0;
 #pragma unroll 1
@@ -282,20 +290,27 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                                     b_lo += (uint32_t)(HBLK2 >> 4) - 2 * (KBLK / 16);
                                 }
                             }
-                            // tensor-memory slot of chunk ss_end: ih * HT + (ss_end - ih * NKB/2 - HS)
-                            uint32_t a_t = tmem_base + W_COL + (uint32_t)((ih * HT + ss_end - ih * (NKB / 2) - HS) * 32);
+                            if constexpr (ss_end < c1) {
+                                // tensor-memory slot of chunk ss_end: ih * HT + (ss_end - ih * NKB/2 - HS)
+                                uint32_t a_t = tmem_base + W_COL + (uint32_t)((ih * HT + ss_end - ih * (NKB / 2) - HS) * 32);
 #pragma unroll 1
-                            for (int c = ss_end; c < c1; ++c) {
+                                for (int c = ss_end; c < c1; ++c) {
 #pragma unroll
-                                for (int k = 0; k < KBLK / 16; ++k) {
-                                    ptx::umma2_f16_ts_warp(d_tmem, a_t, ((uint64_t)b_hi << 32) | b_lo, a.idesc, (c != ih * (NKB / 2) || k != 0) ? 1u : 0u);
-                                    a_t += 8; b_lo += 2;
+                                    for (int k = 0; k < KBLK / 16; ++k) {
+                                        ptx::umma2_f16_ts_warp(d_tmem, a_t, ((uint64_t)b_hi << 32) | b_lo, a.idesc, (c != ih * (NKB / 2) || k != 0) ? 1u : 0u);
+                                        a_t += 8; b_lo += 2;
+                                    }
+                                    b_lo += (uint32_t)(HBLK2 >> 4) - 2 * (KBLK / 16);
                                 }
-                                b_lo += (uint32_t)(HBLK2 >> 4) - 2 * (KBLK / 16);
                             }
                         };
-                        issue_quarter(std::integral_constant<int, 2 * ih>{});
-                        issue_quarter(std::integral_constant<int, 2 * ih + 1>{});
+                        constexpr int P0 = ih * (PARTS / 2);
+                        issue_part(std::integral_constant<int, P0>{});
+                        issue_part(std::integral_constant<int, P0 + 1>{});
+                        if constexpr (PARTS == 8) {
+                            issue_part(std::integral_constant<int, P0 + 2>{});
+                            issue_part(std::integral_constant<int, P0 + 3>{});
+                        }
                         ptx::umma2_commit_warp(&acc_full[g]);       // -> acc_full[g] of BOTH CTAs
                         if (ih == 1 && lane == 0) AVC_TRACE2(g, 9);
                     };
@@ -322,7 +337,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         auto piece_plane = [&](int i) { return WPC2 == 1 ? 2 * (i & 3) + lpl : (wg % WPC2) * (8 / WPC2) + 2 * i + lpl; };
         const __nv_bfloat16* rows_base = yx_tile + (size_t)(crank * SUB_ROWS + lrow) * PLANE_ELEMS;
         auto piece_src = [&](int i) { return rows_base + (size_t)(piece_chunk(i) * 8 + piece_plane(i)) * PSTRIDE; };
-        const int gq = (wg * 4) / GROUP_WARPS;                  // chunk quarter this warp's chunks belong to (warps 2q, 2q+1)
+        const int gp = wg / WPP;                                // the part this warp's chunks belong to
 
         // ---- epilogue geometry ----
         const int q = wg & 3, half = wg >> 2;                 // TMEM lane quarter (= warp % 4); column half (16 utterances)
@@ -400,7 +415,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 }
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive_cluster(&gfull[g * 4 + gq], 0u);     // the LEADER's barrier (both CTAs arrive)
+                if (lane == 0) ptx::mbar_arrive_cluster(&gfull[g * PARTS + gp], 0u);     // the LEADER's barrier (both CTAs arrive)
                 if (tg == 0) AVC_TRACE2(g, 2);
                 if (lane == 0) AVC_TRACE2(g, 16 + wg);
                 stage_gx(t + 1);
@@ -447,10 +462,12 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             }
 #pragma unroll
             for (int k = 0; k < CPT2; ++k)      // after ALL the loads above: a store in the loop would order every Gx read behind it
-                asm volatile("st.shared.f32 [%0], %1;" ::"r"(gt_smem + (uint32_t)((k * 32 + lane) * 4)), "f"(act[k]) : "memory");
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(gt_smem + (uint32_t)((k * 32 + (lane ^ (((k / (CPT2 / 4)) & 3) << 3))) * 4)), "f"(act[k]) : "memory");
             __syncwarp();
             if (tg == 0) AVC_TRACE2(g, 6);
-            // lane j: unit (j >> 2) of this quarter, columns 4 (j & 3) .. + 3 of this half: i, f, g, o as one 16-byte read each
+            // lane j: unit (j >> 2) of this quarter, columns 4 (j & 3) .. + 3 of this half: i, f, g, o as one 16-byte read each.  The
+            // 16-byte granules of a tile row are XOR-swizzled by the row's column group: a quarter-warp reads the rows of four
+            // groups at a 512-byte stride, which unswizzled is a 4-way bank conflict (12.5 M of the launch's 21.5 M load wavefronts).
             constexpr int H2 = CPT2 / 4;
             uint32_t hp[H2 / 2];
 #pragma unroll
@@ -459,7 +476,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 #pragma unroll
                 for (int w = 0; w < 2; ++w) {
                     const int kk = k + w;
-                    const uint4 gates = ld_shared_v4(gt_smem + (uint32_t)(((gj * H2 + kk) * 32 + (lane & ~3)) * 4));
+                    const uint4 gates = ld_shared_v4(gt_smem + (uint32_t)(((gj * H2 + kk) * 32 + ((lane & ~3) ^ (gj << 3))) * 4));
                     const float ig = __uint_as_float(gates.x), fg = __uint_as_float(gates.y), gg = __uint_as_float(gates.z), og = __uint_as_float(gates.w);
                     c[kk] = cell_update(fg, c[kk], ig, gg);
                     float tc;
