@@ -132,7 +132,7 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 // variant the batch size selects): the product i g is rounded, then fused into f c
 __device__ __forceinline__ float cell_update(float fg, float c, float ig, float gg) { return fmaf(fg, c, __fmul_rn(ig, gg)); }
 
-#define AVC_TRACE2(g, pt) do { if (a.trace && blockIdx.x == 0 && blockIdx.y == 0 && t >= TRACE_T0 && t < TRACE_T0 + TRACE_STEPS) \
+#define AVC_TRACE2(g, pt) do { if (tr_cta && (unsigned)(t - TRACE_T0) < (unsigned)TRACE_STEPS) \
     a.trace[((t - TRACE_T0) * 2 + (g)) * TR_PTS + (pt)] = clock64(); } while (0)
 
 template <int NKB, bool GXH, int NSUB>
@@ -175,6 +175,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int ns = blockIdx.x;            // unit slice (32 units)
+    const bool tr_cta = a.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0;      // AVC_LSTM_TRACE=1: CTA (0,0) stamps its steps
     const int bt = blockIdx.y;            // group of NSUB 32-utterance sub-tiles
     const uint32_t crank = ptx::cluster_ctarank();
     const size_t tile_elems = (size_t)a.H * SUB_N;                      // one (t, 32-row tile) block of Yx
@@ -355,20 +356,27 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         // copies exactly the [16 utterances of its half] x [32 gate rows of its lane quarter] block its own lanes read, so the
         // hand-over needs a __syncwarp, not a barrier of the group.  One commit group per step (an empty one past the end), so
         // "all but the newest group" is always "this step's block".  The row index t / gx_div is kept incrementally.
-        int gx_row = 0, gx_left = a.gx_div;       // row of the NEXT block to stage, steps left on that row
+        // Source pointers and destination offsets of the lane's pieces are fixed for the launch: only the row offset moves.
+        constexpr int GX_ES = GXH ? 2 : 4, GX_SEGS = 32 * GX_ES / 16;     // 16-byte pieces per utterance of the warp's block: 4 / 8
+        constexpr int GX_NP = CPT2 * GX_SEGS / 32;                       // pieces per lane and step: 2 / 4
+        const char* gx_src[GX_NP];
+        uint32_t gx_dst[GX_NP];
+#pragma unroll
+        for (int i = 0; i < GX_NP; ++i) {
+            const int u = half * CPT2 + lane / GX_SEGS + (32 / GX_SEGS) * i, seg = lane % GX_SEGS;
+            const int b = b0 + u < a.B ? b0 + u : a.B - 1;
+            gx_src[i] = reinterpret_cast<const char*>(a.Gx) + ((size_t)b * a.gx_sb + (size_t)ns * MROWS + (size_t)(q * 32)) * GX_ES + seg * 16;
+            gx_dst[i] = gx_smem0 + (uint32_t)((u * MROWS + q * 32) * GX_ES + seg * 16);
+        }
+        const size_t gx_row_bytes = (size_t)a.gx_st * GX_ES;
+        size_t gx_off = 0;                        // byte offset of the row of the NEXT block to stage
+        int gx_left = a.gx_div;                   // steps left on that row
         auto stage_gx = [&](int t) {
             if (t < a.T) {
-                const size_t toff = (size_t)gx_row * a.gx_st + (size_t)ns * MROWS + (size_t)(q * 32);
-                constexpr int ES = GXH ? 2 : 4, SEGS = 32 * ES / 16;          // 16-byte pieces per utterance of the warp's block: 4 / 8
-                const uint32_t dst = gx_smem0 + (uint32_t)((t & 1) * GXB);
+                const uint32_t boff = (uint32_t)((t & 1) * GXB);
 #pragma unroll
-                for (int i = 0; i < CPT2 * SEGS / 32; ++i) {
-                    const int u = half * CPT2 + lane / SEGS + (32 / SEGS) * i, seg = lane % SEGS;
-                    const int b = b0 + u < a.B ? b0 + u : a.B - 1;
-                    cp_async16(dst + (uint32_t)((u * MROWS + q * 32) * ES + seg * 16),
-                               reinterpret_cast<const char*>(a.Gx) + ((size_t)b * a.gx_sb + toff) * ES + seg * 16);
-                }
-                if (--gx_left == 0) { ++gx_row; gx_left = a.gx_div; }
+                for (int i = 0; i < GX_NP; ++i) cp_async16(gx_dst[i] + boff, gx_src[i] + gx_off);
+                if (--gx_left == 0) { gx_off += gx_row_bytes; gx_left = a.gx_div; }
             }
             cp_async_commit();
         };
