@@ -132,10 +132,12 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 // variant the batch size selects): the product i g is rounded, then fused into f c
 __device__ __forceinline__ float cell_update(float fg, float c, float ig, float gg) { return fmaf(fg, c, __fmul_rn(ig, gg)); }
 
-#define AVC_TRACE2(g, pt) do { if (tr_cta && (unsigned)(t - TRACE_T0) < (unsigned)TRACE_STEPS) \
+#define AVC_TRACE2(g, pt) do { if (TRACE && tr_cta && (unsigned)(t - TRACE_T0) < (unsigned)TRACE_STEPS) \
     a.trace[((t - TRACE_T0) * 2 + (g)) * TR_PTS + (pt)] = clock64(); } while (0)
 
-template <int NKB, bool GXH, int NSUB>
+// TRACE: the instantiation AVC_LSTM_TRACE=1 launches (clock64 stamps of CTA (0,0)); the production one carries none of it -
+// every instruction on a warp's path through a step costs ~9 cycles of the step (profiles/r2_ll_lstm_notes.md).
+template <int NKB, bool GXH, int NSUB, bool TRACE>
 __global__ void __launch_bounds__(threads(NSUB), 1)
 ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     constexpr int ISSUE_WARP = NSUB * GROUP_WARPS;            // and ISSUE_WARP + 1: one K half each
@@ -175,13 +177,13 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int ns = blockIdx.x;            // unit slice (32 units)
-    const bool tr_cta = a.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0;      // AVC_LSTM_TRACE=1: CTA (0,0) stamps its steps
+    const bool tr_cta = TRACE && a.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0;      // AVC_LSTM_TRACE=1: CTA (0,0) stamps its steps
     const int bt = blockIdx.y;            // group of NSUB 32-utterance sub-tiles
     const uint32_t crank = ptx::cluster_ctarank();
     const size_t tile_elems = (size_t)a.H * SUB_N;                      // one (t, 32-row tile) block of Yx
     const size_t step_elems = tile_elems * a.tiles;
 
-#define AVC_TRACE_PRO(pt) do { if (a.trace && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) a.trace[2 * TRACE_STEPS * TR_PTS + (pt)] = clock64(); } while (0)
+#define AVC_TRACE_PRO(pt) do { if (TRACE && a.trace && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) a.trace[2 * TRACE_STEPS * TR_PTS + (pt)] = clock64(); } while (0)
     AVC_TRACE_PRO(0);
     if (warp == 0) {
         if (lane == 0) {
@@ -337,14 +339,22 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         auto piece_chunk = [&](int i) { return WPC2 == 1 ? wg * CPW + (i >> 2) : wg / WPC2; };
         auto piece_plane = [&](int i) { return WPC2 == 1 ? 2 * (i & 3) + lpl : (wg % WPC2) * (8 / WPC2) + 2 * i + lpl; };
         const __nv_bfloat16* rows_base = yx_tile + (size_t)(crank * SUB_ROWS + lrow) * PLANE_ELEMS;
-        auto piece_src = [&](int i) { return rows_base + (size_t)(piece_chunk(i) * 8 + piece_plane(i)) * PSTRIDE; };
+        // The lane's pieces sit at compile-time distances from its first one; everything that does not depend on t is computed
+        // here, once, and made opaque to the compiler (it would rather rebuild 64-bit addresses every step than hold them).
+        const char* rd_base = reinterpret_cast<const char*>(rows_base + (size_t)(piece_chunk(0) * 8 + piece_plane(0)) * PSTRIDE);
+        asm volatile("" : "+l"(rd_base));
+        auto piece_delta = [](int i) { return (WPC2 == 1 ? (i >> 2) * 8 + 2 * (i & 3) : 2 * i) * PSTRIDE * 2; };      // bytes from piece 0
+        const uint32_t slot_bytes = (uint32_t)(step_elems * 2);      // one ring slot (<= a few MiB)
         const int gp = wg / WPP;                                // the part this warp's chunks belong to
+        uint32_t gfull_remote = ptx::mapa_u32(ptx::smem_u32(&gfull[g * PARTS + gp]), 0u);    // the LEADER's barrier of this warp's part
+        asm volatile("" : "+r"(gfull_remote));
 
         // ---- epilogue geometry ----
         const int q = wg & 3, half = wg >> 2;                 // TMEM lane quarter (= warp % 4); column half (16 utterances)
         const int R = q * 32 + lane;                          // gate row of this CTA = TMEM lane
         const int gj = lane & 3;                              // gate of this lane: 0=i 1=f 2=g 3=o
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(2 * g * SUB_N + half * CPT2);   // K half 1: + SUB_N
+        uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(2 * g * SUB_N + half * CPT2);   // K half 1: + SUB_N
+        asm volatile("" : "+r"(taddr));                       // held in a register (else: rebuilt after every accumulator wait)
         const float act_s = gj == 2 ? 2.0f : 1.0f, act_o = gj == 2 ? -1.0f : 0.0f;
         const uint32_t gt_smem = ptx::smem_u32(sGT) + (uint32_t)(g * GT_BYTES + wg * (16 * 32 * 4));   // this warp's transpose tile
         float c[CPT2 / 4];
@@ -390,6 +400,15 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 return ld_shared_f32(gx_smem + (uint32_t)(((half * CPT2 + k) * MROWS + R) * 4));
             }
         };
+        // h_t store geometry (see the store block below), fixed for the launch
+        const bool wr_odd = (lane >> 2) & 1;
+        const int wr_col = half * CPT2 + gj * (CPT2 / 4) + (wr_odd ? 2 : 0);       // first of the lane's two utterances (within the sub-tile)
+        const int wr_upair = (lane >> 3) * 2;                                       // even unit of the lane's pair, within this quarter's 8
+        char* yx_wr = reinterpret_cast<char*>(yx_tile + ((size_t)(ns * 4 + q) * SUB_N + wr_col) * PLANE_ELEMS + wr_upair);
+        char* y_wr = reinterpret_cast<char*>(a.Y + (size_t)ns * SLICE_UNITS + q * 8 + wr_upair + (size_t)(b0 + wr_col < a.B ? b0 + wr_col : 0) * a.y_sb);
+        asm volatile("" : "+l"(yx_wr), "+l"(y_wr));
+        const bool y_ok0 = b0 + wr_col < a.B, y_ok1 = b0 + wr_col + 1 < a.B;
+        const size_t y_row_bytes = (size_t)a.y_sb * 2, y_step_bytes = (size_t)a.y_st * 2;
         stage_gx(0);
         stage_gx(1);
 
@@ -397,17 +416,17 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             gx_smem = gx_smem0 + (uint32_t)((t & 1) * GXB);
             if (t >= 1) {
                 // ---- h_{t-1} of this sub-tile: L2 -> registers (poll) -> swizzled operand tile ----
-                const size_t soff = (size_t)((t - 1) & 1) * step_elems;                       // ring slot of h_{t-1} ...
+                const char* rd = rd_base + (((t - 1) & 1) ? slot_bytes : 0u);                  // ring slot of h_{t-1} ...
                 const uint32_t etag = (((uint32_t)(t - 1) >> 1) & 1u) * EPOCH_BITS;           // ... and its epoch
                 if (tg == 0) AVC_TRACE2(g, 0);
                 uint4 v[NP];
 #pragma unroll
-                for (int i = 0; i < NP; ++i) v[i] = ld_strong(piece_src(i) + soff);
+                for (int i = 0; i < NP; ++i) v[i] = ld_strong(rd + piece_delta(i));
                 for (uint32_t spin = 0;; ++spin) {          // pieces not written yet: fetch all of them again, together
                     bool missing = false;
 #pragma unroll
                     for (int i = 0; i < NP; ++i)
-                        if (unwritten(v[i], etag)) { v[i] = ld_strong(piece_src(i) + soff); missing = true; }
+                        if (unwritten(v[i], etag)) { v[i] = ld_strong(rd + piece_delta(i)); missing = true; }
                     if (!missing) break;
                     if (spin > (1u << 22)) {
                         printf("autovc_b200: lstm h poll timed out (slice %d tile %d sub %d t %d warp %d lane %d)\n", ns, bt, g, t, wg, lane);
@@ -423,7 +442,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 }
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive_cluster(&gfull[g * PARTS + gp], 0u);     // the LEADER's barrier (both CTAs arrive)
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(gfull_remote) : "memory");   // both CTAs arrive
                 if (tg == 0) AVC_TRACE2(g, 2);
                 if (lane == 0) AVC_TRACE2(g, 16 + wg);
                 stage_gx(t + 1);
@@ -502,14 +521,10 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             // (unit pair) x (two utterances) block, i.e. two 32-bit words: the validity protocol needs whole 32-bit words from one
             // thread (a word with one stale half must not pass the epoch check).  No shared-memory staging, no barrier.
             {
-                const bool odd = (lane >> 2) & 1;
-                const uint32_t mine = odd ? hp[1] : hp[0];
-                const uint32_t theirs = __shfl_xor_sync(0xffffffffu, odd ? hp[0] : hp[1], 4);
-                const uint32_t ev = odd ? theirs : mine, od = odd ? mine : theirs;      // even unit / odd unit, same two utterances
+                const uint32_t mine = wr_odd ? hp[1] : hp[0];
+                const uint32_t theirs = __shfl_xor_sync(0xffffffffu, wr_odd ? hp[0] : hp[1], 4);
+                const uint32_t ev = wr_odd ? theirs : mine, od = wr_odd ? mine : theirs;      // even unit / odd unit, same two utterances
                 const uint32_t w0 = __byte_perm(ev, od, 0x5410), w1 = __byte_perm(ev, od, 0x7632);
-                const int col = half * CPT2 + gj * H2 + (odd ? 2 : 0);                  // first of the two utterances (within the sub-tile)
-                const int upair = (lane >> 3) * 2;                                       // even unit of the pair, within this quarter's 8
-                __nv_bfloat16* yx = yx_tile + (size_t)(t & 1) * step_elems + ((size_t)(ns * 4 + q) * SUB_N + col) * PLANE_ELEMS + upair;
                 if (t + 1 < a.T) {
                     uint32_t x0 = w0, x1 = w1;
                     if ((x0 | x1) & EPOCH_BITS) {      // non-finite h (never for finite inputs): +-1 in the exchange copy, see the header
@@ -521,12 +536,13 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                         x0 = fix(x0); x1 = fix(x1);
                     }
                     const uint32_t ptag = (((uint32_t)t >> 1) & 1u) * EPOCH_BITS;
+                    char* yx = yx_wr + ((t & 1) ? slot_bytes : 0u);
                     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx), "r"(x0 | ptag) : "memory");
-                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx + PLANE_ELEMS), "r"(x1 | ptag) : "memory");
+                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx + PLANE_ELEMS * 2), "r"(x1 | ptag) : "memory");
                 }
-                __nv_bfloat16* y = a.Y + (size_t)t * a.y_st + (size_t)ns * SLICE_UNITS + q * 8 + upair;
-                if (b0 + col < a.B) *reinterpret_cast<uint32_t*>(y + (size_t)(b0 + col) * a.y_sb) = w0;
-                if (b0 + col + 1 < a.B) *reinterpret_cast<uint32_t*>(y + (size_t)(b0 + col + 1) * a.y_sb) = w1;
+                if (y_ok0) *reinterpret_cast<uint32_t*>(y_wr) = w0;
+                if (y_ok1) *reinterpret_cast<uint32_t*>(y_wr + y_row_bytes) = w1;
+                y_wr += y_step_bytes;
             }
             if (tg == 0) AVC_TRACE2(g, 4);
         }
@@ -546,15 +562,18 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode_ll = nullptr;
 
-template <int NSUB>
+template <int NSUB, bool TRACE>
 const void* kernel_for_n(int nkb, bool gxh) {
     switch (nkb) {
-        case 16: return gxh ? (const void*)ll_lstm_kernel<16, true, NSUB> : (const void*)ll_lstm_kernel<16, false, NSUB>;
-        case 8: return gxh ? (const void*)ll_lstm_kernel<8, true, NSUB> : (const void*)ll_lstm_kernel<8, false, NSUB>;
-        default: return gxh ? (const void*)ll_lstm_kernel<4, true, NSUB> : (const void*)ll_lstm_kernel<4, false, NSUB>;
+        case 16: return gxh ? (const void*)ll_lstm_kernel<16, true, NSUB, TRACE> : (const void*)ll_lstm_kernel<16, false, NSUB, TRACE>;
+        case 8: return gxh ? (const void*)ll_lstm_kernel<8, true, NSUB, TRACE> : (const void*)ll_lstm_kernel<8, false, NSUB, TRACE>;
+        default: return gxh ? (const void*)ll_lstm_kernel<4, true, NSUB, TRACE> : (const void*)ll_lstm_kernel<4, false, NSUB, TRACE>;
     }
 }
-const void* kernel_for(int nkb, bool gxh, int nsub) { return nsub == 2 ? kernel_for_n<2>(nkb, gxh) : kernel_for_n<1>(nkb, gxh); }
+const void* kernel_for(int nkb, bool gxh, int nsub, bool trace = false) {
+    if (trace) return nsub == 2 ? kernel_for_n<2, true>(nkb, gxh) : kernel_for_n<1, true>(nkb, gxh);
+    return nsub == 2 ? kernel_for_n<2, false>(nkb, gxh) : kernel_for_n<1, false>(nkb, gxh);
+}
 int smem_for(int nkb, bool gxh, int nsub) {
     const int nkb_s = nkb > max_tmem_chunks(nsub) ? nkb - max_tmem_chunks(nsub) : 0;
     return nkb_s * W_BLK_BYTES + nsub * (nkb * HBLK2 + 2 * gx2_bytes(gxh) + GT_BYTES) + 1024 + 512;
@@ -584,8 +603,9 @@ const char* ll_lstm_init() {
         const int nkb = 4 << ((i >> 1) % 3), nsub = i < 6 ? 1 : 2;
         const int bytes = smem_for(nkb, i & 1, nsub);
         if (bytes > SMEM_LIMIT) continue;          // H = 1024, two sub-tiles, fp32 Gx does not fit: such a plan takes one sub-tile
-        if (cudaFuncSetAttribute(kernel_for(nkb, i & 1, nsub), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
-            return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed for ll_lstm_kernel";
+        for (int tr = 0; tr < 2; ++tr)
+            if (cudaFuncSetAttribute(kernel_for(nkb, i & 1, nsub, tr), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
+                return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed for ll_lstm_kernel";
     }
     g_encode_ll = reinterpret_cast<EncodeTiledFn>(fn);
     return nullptr;
@@ -660,7 +680,7 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
         void* kargs[2] = {(void*)&plan->tmW, (void*)&args};
         // CTAs wait on one another's output: cooperative launch (guaranteed co-residency), with the checked non-cooperative
         // retry of launch_persistent() for profilers (AVC_LSTM_NOCOOP forces it)
-        e = launch_persistent(kernel_for(plan->nkb, plan->gx_f16, plan->nsub), plan->grids[i], dim3(threads(plan->nsub)), (size_t)plan->smem_bytes, 2,
+        e = launch_persistent(kernel_for(plan->nkb, plan->gx_f16, plan->nsub, tracing), plan->grids[i], dim3(threads(plan->nsub)), (size_t)plan->smem_bytes, 2,
                               kargs, s, getenv("AVC_LSTM_NOCOOP") != nullptr);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
