@@ -132,6 +132,27 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 // variant the batch size selects): the product i g is rounded, then fused into f c
 __device__ __forceinline__ float cell_update(float fg, float c, float ig, float gg) { return fmaf(fg, c, __fmul_rn(ig, gg)); }
 
+// packed fp32 pairs (sm_100): two IEEE adds / fmas in one issue slot, bit-identical to the scalar instructions
+__device__ __forceinline__ void add_f32x2(float& a0, float& a1, float b0, float b1) {
+    asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tadd.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void fma_f32x2(float& a0, float& a1, float m, float c) {      // a = m * a + c on both
+    asm("{\n\t.reg .b64 x, y, z;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %2};\n\tmov.b64 z, {%3, %3};\n\tfma.rn.f32x2 x, y, x, z;\n\tmov.b64 {%0, %1}, x;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(m), "f"(c));
+}
+
+__device__ __forceinline__ void mul_f32x2(float& a0, float& a1, float b0, float b1) {
+    asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tmul.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+// c' = f c + i g for two cells, the rounding order of cell_update()
+__device__ __forceinline__ void cell_update_x2(float& c0, float& c1, float f0, float f1, float i0, float i1, float g0, float g1) {
+    asm("{\n\t.reg .b64 c, f, i, g;\n\tmov.b64 c, {%0, %1};\n\tmov.b64 f, {%2, %3};\n\tmov.b64 i, {%4, %5};\n\tmov.b64 g, {%6, %7};\n\t"
+        "mul.rn.f32x2 i, i, g;\n\tfma.rn.f32x2 c, f, c, i;\n\tmov.b64 {%0, %1}, c;\n\t}"
+        : "+f"(c0), "+f"(c1) : "f"(f0), "f"(f1), "f"(i0), "f"(i1), "f"(g0), "f"(g1));
+}
+
 #define AVC_TRACE2(g, pt) do { if (TRACE && tr_cta && (unsigned)(t - TRACE_T0) < (unsigned)TRACE_STEPS) \
     a.trace[((t - TRACE_T0) * 2 + (g)) * TR_PTS + (pt)] = clock64(); } while (0)
 
@@ -452,6 +473,10 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             asm volatile("cp.async.wait_group 1;" ::: "memory");     // own pieces of Gx_t (the newest group is Gx_{t+1}) ...
             __syncwarp();                                            // ... and the other lanes' (the block is this warp's alone)
             if (tg == 0) AVC_TRACE2(g, 26);
+            // Gx_t of this lane's row, fetched and converted BEFORE the accumulator wait: 32 instructions off the critical path
+            float gxv[CPT2];
+#pragma unroll
+            for (int k = 0; k < CPT2; ++k) gxv[k] = gx_at(k);
             float act[CPT2];
             if (t >= 1) {
                 ptx::mbar_wait(my_acc, (uint32_t)(t - 1) & 1);
@@ -464,53 +489,60 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 ptx::tc_fence_before();
                 if (tg == 0) AVC_TRACE2(g, 5);
 #pragma unroll
-                for (int k = 0; k < CPT2; ++k) act[k] = __uint_as_float(acc0[k]) + __uint_as_float(acc1[k]);
+                for (int k = 0; k < CPT2; k += 2) {        // (acc0 + acc1) + Gx, in this order
+                    act[k] = __uint_as_float(acc0[k]); act[k + 1] = __uint_as_float(acc0[k + 1]);
+                    add_f32x2(act[k], act[k + 1], __uint_as_float(acc1[k]), __uint_as_float(acc1[k + 1]));
+                    add_f32x2(act[k], act[k + 1], gxv[k], gxv[k + 1]);
+                }
             } else {
 #pragma unroll
-                for (int k = 0; k < CPT2; ++k) act[k] = 0.0f;
+                for (int k = 0; k < CPT2; ++k) act[k] = 0.0f + gxv[k];
             }
             // gate activation of this lane's row (x' already is the tanh argument, see pack_lstm), written to the warp's transpose
             // tile [column][gate row]: the four gates of a unit are four consecutive floats there
             if (a.approx) {
                 const float ps = gj == 2 ? 1.0f : 0.5f, po = gj == 2 ? 0.0f : 0.5f;
 #pragma unroll
-                for (int k = 0; k < CPT2; ++k) {
-                    const float x = act[k] + gx_at(k);
-                    float th;
-                    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(x));
-                    act[k] = fmaf(ps, th, po);
+                for (int k = 0; k < CPT2; k += 2) {
+                    asm("tanh.approx.f32 %0, %0;" : "+f"(act[k]));
+                    asm("tanh.approx.f32 %0, %0;" : "+f"(act[k + 1]));
+                    fma_f32x2(act[k], act[k + 1], ps, po);
                 }
             } else {
 #pragma unroll
-                for (int k = 0; k < CPT2; ++k) {
-                    const float x = act[k] + gx_at(k);
-                    act[k] = __fdividef(act_s, 1.0f + __expf(-2.0f * x)) + act_o;
-                }
+                for (int k = 0; k < CPT2; ++k) act[k] = __fdividef(act_s, 1.0f + __expf(-2.0f * act[k])) + act_o;
             }
+            // Transpose tile of the warp, 8 rows (column PAIRS) x 256 bytes: row p holds, per unit u of the lane quarter, the floats
+            // [i_k i_k+1 f_k f_k+1 | g_k g_k+1 o_k o_k+1] of columns k = 2p, 2p+1 - a lane (gate row 4u + j) stores its pair as one
+            // 8-byte word, a reader (unit, column group) gets every operand of the two cells as an adjacent register pair for the
+            // packed fp32x2 instructions.  The 16-byte granules of a row are XOR-swizzled by the row's column group: a quarter-warp
+            // reads the rows of four groups at a 512-byte stride - unswizzled a 4-way bank conflict (12.5 M of the launch's 21.5 M
+            // shared-load wavefronts were such conflicts).
+            static_assert(CPT2 == 16, "tile geometry below is written for 16 columns per thread");
+            auto gt_swz = [](int grp) { return (uint32_t)((grp & 1) | ((grp & 2) << 1)); };      // 0, 1, 4, 5
 #pragma unroll
-            for (int k = 0; k < CPT2; ++k)      // after ALL the loads above: a store in the loop would order every Gx read behind it
-                asm volatile("st.shared.f32 [%0], %1;" ::"r"(gt_smem + (uint32_t)((k * 32 + (lane ^ (((k / (CPT2 / 4)) & 3) << 3))) * 4)), "f"(act[k]) : "memory");
+            for (int kp = 0; kp < CPT2 / 2; ++kp)
+                asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(gt_smem + (uint32_t)(kp * 256) + ((((uint32_t)lane >> 1) ^ gt_swz(kp >> 1)) << 4) + (uint32_t)((lane & 1) << 3)),
+                             "f"(act[2 * kp]), "f"(act[2 * kp + 1]) : "memory");
             __syncwarp();
             if (tg == 0) AVC_TRACE2(g, 6);
-            // lane j: unit (j >> 2) of this quarter, columns 4 (j & 3) .. + 3 of this half: i, f, g, o as one 16-byte read each.  The
-            // 16-byte granules of a tile row are XOR-swizzled by the row's column group: a quarter-warp reads the rows of four
-            // groups at a 512-byte stride, which unswizzled is a 4-way bank conflict (12.5 M of the launch's 21.5 M load wavefronts).
+            // lane j: unit (j >> 2) of this quarter, columns 4 (j & 3) .. + 3 of this half
             constexpr int H2 = CPT2 / 4;
             uint32_t hp[H2 / 2];
+            const uint32_t gt_rd = gt_smem + (uint32_t)(gj * 512) + (((uint32_t)(lane >> 2) * 2u) ^ gt_swz(gj)) * 16u;      // (i, f) granule; (g, o): ^ 16
 #pragma unroll
             for (int k = 0; k < H2; k += 2) {
+                const uint4 gif = ld_shared_v4(gt_rd + (uint32_t)((k >> 1) * 256));               // i_k i_k+1 f_k f_k+1
+                const uint4 ggo = ld_shared_v4((gt_rd ^ 16u) + (uint32_t)((k >> 1) * 256));        // g_k g_k+1 o_k o_k+1
+                cell_update_x2(c[k], c[k + 1], __uint_as_float(gif.z), __uint_as_float(gif.w), __uint_as_float(gif.x), __uint_as_float(gif.y),
+                               __uint_as_float(ggo.x), __uint_as_float(ggo.y));
                 float hv[2];
 #pragma unroll
                 for (int w = 0; w < 2; ++w) {
-                    const int kk = k + w;
-                    const uint4 gates = ld_shared_v4(gt_smem + (uint32_t)(((gj * H2 + kk) * 32 + ((lane & ~3) ^ (gj << 3))) * 4));
-                    const float ig = __uint_as_float(gates.x), fg = __uint_as_float(gates.y), gg = __uint_as_float(gates.z), og = __uint_as_float(gates.w);
-                    c[kk] = cell_update(fg, c[kk], ig, gg);
-                    float tc;
-                    if (a.approx) asm("tanh.approx.f32 %0, %1;" : "=f"(tc) : "f"(c[kk]));
-                    else tc = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * c[kk]));
-                    hv[w] = og * tc;
+                    if (a.approx) asm("tanh.approx.f32 %0, %1;" : "=f"(hv[w]) : "f"(c[k + w]));
+                    else hv[w] = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * c[k + w]));
                 }
+                mul_f32x2(hv[0], hv[1], __uint_as_float(ggo.z), __uint_as_float(ggo.w));          // h = tanh(c') o
                 __nv_bfloat162 h2 = __floats2bfloat162_rn(hv[0], hv[1]);
                 hp[k >> 1] = *reinterpret_cast<uint32_t*>(&h2);
             }
