@@ -135,6 +135,17 @@ __device__ __forceinline__ void cluster_sync() {
 
 // ---- CTA pairs (cta_group::2) -----------------------------------------------------------------
 // address of `local` (a shared::cta address of this CTA) in the shared::cluster window of CTA `rank`
+// packed fp32 pairs (sm_100): two IEEE adds in one issue slot, bit-identical to two scalar FADDs
+__device__ __forceinline__ void add_f32x2(float& a0, float& a1, float b0, float b1) {
+    asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tadd.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+// ReLU that keeps a NaN a NaN like torch.relu (fmaxf(NaN, 0) is 0): one FMNMX.NAN instead of a compare and a select
+__device__ __forceinline__ float relu_nan(float v) {
+    float r;
+    asm("max.NaN.f32 %0, %1, 0f00000000;" : "=f"(r) : "f"(v));
+    return r;
+}
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
     uint32_t r;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));

@@ -46,6 +46,8 @@ struct TcGemmArgs {
     double* stat_partial;                // STATS kernels: per (M tile, epilogue warp) column sums / sums of squares [chunk][2][N]
 };
 
+constexpr int ZERO_BIAS_N = 8192;
+__device__ float g_zero_bias[ZERO_BIAS_N];        // zero-initialised: the bias of layers that have none
 constexpr int OUT_STAGE_BYTES = 32 * 128;         // one epilogue warp's 32 rows x 128 bytes, SWIZZLE_128B
 constexpr int OUT_STAGING_BYTES = 4 * 2 * OUT_STAGE_BYTES;   // 4 epilogue warps, double-buffered
 
@@ -184,23 +186,30 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             size_t ot_base = 0;
             if (a.out_t) { const size_t bb = m / a.T, tt = m - bb * a.T; ot_base = (bb * a.N) * a.T + tt; }
 
-            // bias of a 16-column group, loaded ONE GROUP AHEAD (the first before the accumulator wait): consumed straight after
-            // its load it was the epilogue's top stall (ncu source counters: 13 % of the kernel's samples on the first FADD)
+            // bias of a 16-column group, loaded AHEAD of its use (the first before the accumulator wait): consumed straight after
+            // its load it was the epilogue's top stall (ncu source counters: 13 % of the kernel's samples on the first FADD).  A layer
+            // without bias reads a zero vector (g_zero_bias), so the load is unconditional.
             float4 bnext[4];
             auto load_bias = [&](int n) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    bnext[j] = brow ? __ldg(reinterpret_cast<const float4*>(brow + n) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int j = 0; j < 4; ++j) bnext[j] = __ldg(reinterpret_cast<const float4*>(brow + n) + j);
             };
-            load_bias(n0);
-            ptx::mbar_wait(&tfull[as], aphase);
-            ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE);
-            if (a.tma_out) {
-                // Row-major output: each warp stages 32 rows x 128 bytes (XOR-swizzled 16-byte pieces: conflict-free for the
-                // row-per-lane writes) and one lane hands the box to TMA - full-line global writes instead of 32 rows x 16 B
-                // per store instruction.  Two staging buffers per warp; rows beyond the tensor are clipped by the TMA unit.
-                const int cw = a.out_type == DT_F32 ? 32 : 64;               // columns per 128-byte staging row
+            // Row-major output through TMA: each warp stages 32 rows x 128 bytes (XOR-swizzled 16-byte pieces: conflict-free for the
+            // row-per-lane writes) and one lane hands the box to TMA - full-line global writes instead of 32 rows x 16 B per store
+            // instruction.  Two staging buffers per warp; rows beyond the tensor are clipped by the TMA unit.  NG = 16-column
+            // groups per staging row (4 for 16-bit outputs, 2 for fp32), unrolled: the bias of group g of the NEXT block is
+            // requested as soon as group g of this block has used its registers - a whole block (>= 300 cycles) ahead.
+            auto epilogue_tma = [&](auto NG_) {
+                constexpr int NG = decltype(NG_)::value;
+                constexpr int cw = NG * 16;                                  // columns per 128-byte staging row
+                float4 bs[NG][4];
+#pragma unroll
+                for (int g2 = 0; g2 < NG; ++g2)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) bs[g2][j] = 16 * g2 < bn ? __ldg(reinterpret_cast<const float4*>(brow + n0 + 16 * g2) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                ptx::mbar_wait(&tfull[as], aphase);
+                ptx::tc_fence_after();
                 const int r0 = q * 32;
                 const int ct = (mt % a.tiles_t) * a.TB + r0 % a.TB, cb = (mt / a.tiles_t) * a.BB + r0 / a.TB;
                 uint8_t* stg = sOut + q * 2 * OUT_STAGE_BYTES;
@@ -210,30 +219,32 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const uint32_t buf = (uint32_t)((c0 / cw) & 1) * OUT_STAGE_BYTES;
                     if (lane == 0) ptx::bulk_wait_group_read<1>();           // the store that last read this buffer is done
                     __syncwarp();
-#pragma unroll 1
-                    for (int sub = 0; sub < cw; sub += 16) {
+#pragma unroll
+                    for (int g2 = 0; g2 < NG; ++g2) {
+                        const int sub = 16 * g2;
                         uint32_t rr[16];
                         ptx::tmem_ld16(taddr + (uint32_t)(c0 + sub), rr);
-                        const float4 bcur[4] = {bnext[0], bnext[1], bnext[2], bnext[3]};
-                        if (c0 + sub + 16 < bn) load_bias(n0 + c0 + sub + 16);
                         ptx::tmem_ld_wait();
                         float v[16];
 #pragma unroll
                         for (int j = 0; j < 16; j += 4) {
-                            const float4 bv = bcur[j >> 2];
-                            v[j + 0] = __uint_as_float(rr[j + 0]) + bv.x;
-                            v[j + 1] = __uint_as_float(rr[j + 1]) + bv.y;
-                            v[j + 2] = __uint_as_float(rr[j + 2]) + bv.z;
-                            v[j + 3] = __uint_as_float(rr[j + 3]) + bv.w;
+                            v[j + 0] = __uint_as_float(rr[j + 0]); v[j + 1] = __uint_as_float(rr[j + 1]);
+                            v[j + 2] = __uint_as_float(rr[j + 2]); v[j + 3] = __uint_as_float(rr[j + 3]);
+                            ptx::add_f32x2(v[j + 0], v[j + 1], bs[g2][j >> 2].x, bs[g2][j >> 2].y);
+                            ptx::add_f32x2(v[j + 2], v[j + 3], bs[g2][j >> 2].z, bs[g2][j >> 2].w);
+                        }
+                        if (c0 + cw + sub < bn) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) bs[g2][j] = __ldg(reinterpret_cast<const float4*>(brow + n0 + c0 + cw + sub) + j);
                         }
                         if (a.act == ACT_RELU) {
 #pragma unroll
-                            for (int j = 0; j < 16; ++j) v[j] = v[j] < 0.0f ? 0.0f : v[j];     // like torch.relu: a NaN stays a NaN (fmaxf would return 0)
+                            for (int j = 0; j < 16; ++j) v[j] = ptx::relu_nan(v[j]);     // like torch.relu: a NaN stays a NaN (fmaxf would return 0)
                         } else if (a.act == ACT_TANH) {
 #pragma unroll
                             for (int j = 0; j < 16; ++j) v[j] = fast_tanh(v[j]);
                         }
-                        if (a.out_type == DT_F32) {
+                        if constexpr (NG == 2) {
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
                                 const uint32_t piece = (uint32_t)(sub / 4 + j);
@@ -288,7 +299,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         *reinterpret_cast<float2*>(pp + a.N) = make_float2(shift, (float)__popc(vmask));
                     }
                 }
-            } else
+            };
+            if (a.tma_out) {
+                if (a.out_type == DT_F32) epilogue_tma(std::integral_constant<int, 2>{}); else epilogue_tma(std::integral_constant<int, 4>{});
+            } else {
+            load_bias(n0);
+            ptx::mbar_wait(&tfull[as], aphase);
+            ptx::tc_fence_after();
 #pragma unroll 1
             for (int c0 = 0; c0 < bn; c0 += 16) {
                 uint32_t rr[16];
@@ -344,6 +361,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         for (int j = 0; j < 16; ++j) a.out_t[ot_base + (size_t)(n + j) * a.T] = v[j] + rv[j];
                     }
                 }
+            }
             }
             ptx::tc_fence_before();
             ptx::mbar_arrive(&tempty[as]);
@@ -410,7 +428,15 @@ TcGemmPlan* tc_gemm_plan_create(const GemmParams& p, int num_sms, const char** e
     a.N = p.N; a.taps = p.taps; a.Cp = p.Cp; a.pad = p.taps / 2;
     a.kblocks_per_tap = ceil_div(p.taps == 1 ? p.K : p.Cp, BLOCK_K);
     a.T = p.T;
-    a.bias = p.bias; a.row_bias = p.row_bias; a.act = p.act; a.out = p.out; a.out_type = p.out_type; a.ldo = p.ldo; a.out_t = p.out_t; a.res_t = p.res_t;
+    a.bias = p.bias; a.row_bias = p.row_bias;
+    if (!a.bias && !a.row_bias) {            // the epilogue loads its bias unconditionally: a layer without one adds zeros
+        void* z = nullptr;
+        if (p.N > ZERO_BIAS_N || cudaGetSymbolAddress(&z, g_zero_bias) != cudaSuccess) {
+            delete plan;
+            return bad("no zero bias vector for this layer (N too large or cudaGetSymbolAddress failed)");
+        }
+        a.bias = static_cast<const float*>(z);
+    } a.act = p.act; a.out = p.out; a.out_type = p.out_type; a.ldo = p.ldo; a.out_t = p.out_t; a.res_t = p.res_t;
 
     // ---- M tiling: tile = BB utterances x TB frames, TB*BB = 128 ----
     if (p.taps == 1) { a.gT = p.M; a.gB = 1; a.TB = BLOCK_M; a.BB = 1; }
