@@ -24,8 +24,9 @@
 //       the stores; profiles/r2_ll_lstm_notes.md.)  Hence the Gx_t block is staged warp-privately, the 4x4 gate transpose goes
 //       through a per-warp shared-memory tile, and h_t leaves straight from registers.
 //
-// Warp roles (NSUB x 8 + 2 warps):
-//   warps 8g..8g+7   sub-tile g: loaders of its h_{t-1} rows (poll -> swizzled K-major operand tile -> fence.proxy.async ->
+// Warp roles (NSUB x GW + 2 warps; GW = 8 group warps per sub-tile, 16 for the one sub-tile of an H = 1024 CTA - each warp then
+// owns half the chunks and half the columns):
+//   warps GW g..GW g + GW - 1   sub-tile g: loaders of its h_{t-1} rows (poll -> swizzled K-major operand tile -> fence.proxy.async ->
 //                    arrive on the mbarrier of its own K part in the leader CTA) AND its gate epilogue (tcgen05.ld of 16 columns per
 //                    thread, + Gx_t, MUFU.TANH gates, cell update with c in registers, h_t stores)
 //   last two warps   MMA issuers (leader CTA), one K half each into its own accumulator, each strictly alternating
@@ -77,11 +78,13 @@ constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t EPOCH_BITS = 0x40004000u;          // bit 14 of both bf16 halves of a 32-bit word: the step epoch of the exchange ring
 constexpr int SUB_N = 32;                 // utterances per (sub-)tile = UMMA N
 constexpr int SUB_ROWS = SUB_N / 2;       // rows of h staged per CTA and sub-tile
-constexpr int GROUP_WARPS = 8;            // loader + epilogue warps per sub-tile
-constexpr int GT_BYTES = GROUP_WARPS * 16 * 32 * 4;  // 16 KiB per sub-tile: per warp a [16 columns][32 gate rows] fp32 transpose tile
+// loader + epilogue warps per sub-tile: 8, or 16 when an H = 1024 CTA has ONE sub-tile (half the columns, pieces and
+// transcendental chain per warp on the step's critical path: config 3 lstm2 4.45 -> 4.28 ms, B = 1 p50 -1.5 %; at H = 512 the
+// extra pollers cost more than they return: 1.755 -> 1.770 ms)
+__host__ __device__ constexpr int group_warps(int nsub, int nkb) { return nsub == 1 && nkb == 16 ? 16 : 8; }
+constexpr int GT_BYTES = SUB_N * MROWS * 4;          // 16 KiB per sub-tile: the group's [32 columns][128 gate rows] fp32 transpose tiles
 constexpr int HBLK2 = SUB_ROWS * KBLK * 2;           // 2 KiB per CTA, sub-tile and chunk of the operand tile
-constexpr int CPT2 = SUB_N / 2;           // accumulator columns per epilogue thread
-__host__ __device__ constexpr int threads(int nsub) { return (nsub * GROUP_WARPS + 2) * 32; }          // + the two issuer warps: 320 / 576
+__host__ __device__ constexpr int threads(int nsub, int nkb) { return (nsub * group_warps(nsub, nkb) + 2) * 32; }    // + the two issuer warps: 320 / 576
 __host__ __device__ constexpr int max_tmem_chunks(int nsub) { return (512 - 2 * nsub * SUB_N) / 32; }   // two accumulators per sub-tile: 14 / 12
 __host__ __device__ constexpr int gx2_bytes(bool gxh) { return SUB_N * MROWS * (gxh ? 2 : 4); }         // one Gx_t block of a sub-tile: 8 / 16 KiB
 
@@ -159,8 +162,10 @@ __device__ __forceinline__ void cell_update_x2(float& c0, float& c1, float f0, f
 // TRACE: the instantiation AVC_LSTM_TRACE=1 launches (clock64 stamps of CTA (0,0)); the production one carries none of it -
 // every instruction on a warp's path through a step costs ~9 cycles of the step (profiles/r2_ll_lstm_notes.md).
 template <int NKB, bool GXH, int NSUB, bool TRACE>
-__global__ void __launch_bounds__(threads(NSUB), 1)
+__global__ void __launch_bounds__(threads(NSUB, NKB), 1)
 ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
+    constexpr int GROUP_WARPS = group_warps(NSUB, NKB);
+    constexpr int CPT2 = SUB_N * 4 / GROUP_WARPS;             // accumulator columns per epilogue thread: 8 or 16
     constexpr int ISSUE_WARP = NSUB * GROUP_WARPS;            // and ISSUE_WARP + 1: one K half each
     constexpr uint32_t D_COLS2 = 2 * NSUB * SUB_N;            // accumulator of (sub-tile g, K half ih) at columns (2 g + ih) * 32
     constexpr int MAX_TMEM_CHUNKS2 = max_tmem_chunks(NSUB);
@@ -188,11 +193,11 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
     uint64_t* wst_full = bars + 22;                            // [2] prologue: a 16 KiB chunk of W_hh has landed in staging buffer i
     uint64_t* wst_empty = bars + 24;                           // [2] ... and has been moved on to tensor memory
-    // K is handed to the issuers in PARTS pieces.  One sub-tile: eight, each the chunks ONE loader warp of either CTA fills - the
+    // K is handed to the issuers in PARTS pieces.  One sub-tile: eight, each the chunks of two loader warps of either CTA - the
     // MMAs left to issue when the last piece of h_{t-1} lands are an eighth of the step's (same-box A/B: config 3 9.75 -> 9.57 ms,
     // B = 1 p50 1.18 -> 1.16 ms).  Two sub-tiles (and H = 256): quarters - there the issuers share their schedulers with the other
     // sub-tile's epilogue, and twice the barrier waits cost more issue slots than the shorter tail returns (lstm2 0.875 -> 0.90 ms).
-    constexpr int PARTS = (NSUB == 1 && NKB >= GROUP_WARPS) ? GROUP_WARPS : 4;
+    constexpr int PARTS = (NSUB == 1 && NKB >= 8) ? 8 : 4;
     constexpr int WPP = GROUP_WARPS / PARTS;                           // loader warps per part in each CTA
     constexpr int CPP = NKB / PARTS;                                   // chunks per part: 4, 2 or 1
 
@@ -346,7 +351,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         }
     } else {
         // ===================== sub-tile group g: loaders + epilogue =====================
-        const int g = warp >> 3, wg = warp & 7;
+        const int g = warp / GROUP_WARPS, wg = warp % GROUP_WARPS;
         const int tg = (int)(threadIdx.x & ((GROUP_WARPS * 32) - 1));
         const int b0 = (bt * NSUB + g) * SUB_N;
         __nv_bfloat16* yx_tile = a.Yx + (size_t)(a.tile0 + bt * NSUB + g) * tile_elems;    // + t * step_elems
@@ -371,13 +376,13 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         asm volatile("" : "+r"(gfull_remote));
 
         // ---- epilogue geometry ----
-        const int q = wg & 3, half = wg >> 2;                 // TMEM lane quarter (= warp % 4); column half (16 utterances)
+        const int q = wg & 3, half = wg >> 2;                 // TMEM lane quarter (= warp % 4); block of CPT2 columns (utterances)
         const int R = q * 32 + lane;                          // gate row of this CTA = TMEM lane
         const int gj = lane & 3;                              // gate of this lane: 0=i 1=f 2=g 3=o
         uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(2 * g * SUB_N + half * CPT2);   // K half 1: + SUB_N
         asm volatile("" : "+r"(taddr));                       // held in a register (else: rebuilt after every accumulator wait)
         const float act_s = gj == 2 ? 2.0f : 1.0f, act_o = gj == 2 ? -1.0f : 0.0f;
-        const uint32_t gt_smem = ptx::smem_u32(sGT) + (uint32_t)(g * GT_BYTES + wg * (16 * 32 * 4));   // this warp's transpose tile
+        const uint32_t gt_smem = ptx::smem_u32(sGT) + (uint32_t)(g * GT_BYTES + wg * (CPT2 * 32 * 4));   // this warp's transpose tile
         float c[CPT2 / 4];
 #pragma unroll
         for (int k = 0; k < CPT2 / 4; ++k) c[k] = 0.0f;
@@ -423,12 +428,13 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
         };
         // h_t store geometry (see the store block below), fixed for the launch
         const bool wr_odd = (lane >> 2) & 1;
-        const int wr_col = half * CPT2 + gj * (CPT2 / 4) + (wr_odd ? 2 : 0);       // first of the lane's two utterances (within the sub-tile)
+        constexpr int HW = CPT2 / 8;                                                // 32-bit words (utterances) a lane stores per step: 2 or 1
+        const int wr_col = half * CPT2 + gj * (CPT2 / 4) + (wr_odd ? HW : 0);       // first of the lane's HW utterances (within the sub-tile)
         const int wr_upair = (lane >> 3) * 2;                                       // even unit of the lane's pair, within this quarter's 8
         char* yx_wr = reinterpret_cast<char*>(yx_tile + ((size_t)(ns * 4 + q) * SUB_N + wr_col) * PLANE_ELEMS + wr_upair);
         char* y_wr = reinterpret_cast<char*>(a.Y + (size_t)ns * SLICE_UNITS + q * 8 + wr_upair + (size_t)(b0 + wr_col < a.B ? b0 + wr_col : 0) * a.y_sb);
         asm volatile("" : "+l"(yx_wr), "+l"(y_wr));
-        const bool y_ok0 = b0 + wr_col < a.B, y_ok1 = b0 + wr_col + 1 < a.B;
+        const bool y_ok0 = b0 + wr_col < a.B, y_ok1 = HW == 2 && b0 + wr_col + 1 < a.B;
         const size_t y_row_bytes = (size_t)a.y_sb * 2, y_step_bytes = (size_t)a.y_st * 2;
         stage_gx(0);
         stage_gx(1);
@@ -465,7 +471,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 __syncwarp();
                 if (lane == 0) asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(gfull_remote) : "memory");   // both CTAs arrive
                 if (tg == 0) AVC_TRACE2(g, 2);
-                if (lane == 0) AVC_TRACE2(g, 16 + wg);
+                if (lane == 0 && wg < 8) AVC_TRACE2(g, 16 + wg);
                 stage_gx(t + 1);
             }
             // ---- epilogue: gates, cell state, h_t ----
@@ -482,9 +488,14 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 ptx::mbar_wait(my_acc, (uint32_t)(t - 1) & 1);
                 if (tg == 0) AVC_TRACE2(g, 3);
                 ptx::tc_fence_after();
-                uint32_t acc0[16], acc1[16];
-                ptx::tmem_ld16(taddr, acc0);
-                ptx::tmem_ld16(taddr + (uint32_t)SUB_N, acc1);
+                uint32_t acc0[CPT2], acc1[CPT2];
+                if constexpr (CPT2 == 16) {
+                    ptx::tmem_ld16(taddr, acc0);
+                    ptx::tmem_ld16(taddr + (uint32_t)SUB_N, acc1);
+                } else {
+                    ptx::tmem_ld8(taddr, acc0);
+                    ptx::tmem_ld8(taddr + (uint32_t)SUB_N, acc1);
+                }
                 ptx::tmem_ld_wait();
                 ptx::tc_fence_before();
                 if (tg == 0) AVC_TRACE2(g, 5);
@@ -512,24 +523,24 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
 #pragma unroll
                 for (int k = 0; k < CPT2; ++k) act[k] = __fdividef(act_s, 1.0f + __expf(-2.0f * act[k])) + act_o;
             }
-            // Transpose tile of the warp, 8 rows (column PAIRS) x 256 bytes: row p holds, per unit u of the lane quarter, the floats
+            // Transpose tile of the warp, CPT2 / 2 rows (column PAIRS) x 256 bytes: row p holds, per unit u of the lane quarter, the floats
             // [i_k i_k+1 f_k f_k+1 | g_k g_k+1 o_k o_k+1] of columns k = 2p, 2p+1 - a lane (gate row 4u + j) stores its pair as one
             // 8-byte word, a reader (unit, column group) gets every operand of the two cells as an adjacent register pair for the
             // packed fp32x2 instructions.  The 16-byte granules of a row are XOR-swizzled by the row's column group: a quarter-warp
             // reads the rows of four groups at a 512-byte stride - unswizzled a 4-way bank conflict (12.5 M of the launch's 21.5 M
             // shared-load wavefronts were such conflicts).
-            static_assert(CPT2 == 16, "tile geometry below is written for 16 columns per thread");
+            static_assert(CPT2 == 16 || CPT2 == 8, "tile geometry below: 4 or 2 columns per lane in the cell stage");
             auto gt_swz = [](int grp) { return (uint32_t)((grp & 1) | ((grp & 2) << 1)); };      // 0, 1, 4, 5
 #pragma unroll
             for (int kp = 0; kp < CPT2 / 2; ++kp)
-                asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(gt_smem + (uint32_t)(kp * 256) + ((((uint32_t)lane >> 1) ^ gt_swz(kp >> 1)) << 4) + (uint32_t)((lane & 1) << 3)),
+                asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(gt_smem + (uint32_t)(kp * 256) + ((((uint32_t)lane >> 1) ^ gt_swz(kp / (CPT2 / 8))) << 4) + (uint32_t)((lane & 1) << 3)),
                              "f"(act[2 * kp]), "f"(act[2 * kp + 1]) : "memory");
             __syncwarp();
             if (tg == 0) AVC_TRACE2(g, 6);
             // lane j: unit (j >> 2) of this quarter, columns 4 (j & 3) .. + 3 of this half
             constexpr int H2 = CPT2 / 4;
             uint32_t hp[H2 / 2];
-            const uint32_t gt_rd = gt_smem + (uint32_t)(gj * 512) + (((uint32_t)(lane >> 2) * 2u) ^ gt_swz(gj)) * 16u;      // (i, f) granule; (g, o): ^ 16
+            const uint32_t gt_rd = gt_smem + (uint32_t)(gj * (H2 / 2) * 256) + (((uint32_t)(lane >> 2) * 2u) ^ gt_swz(gj)) * 16u;      // (i, f) granule; (g, o): ^ 16
 #pragma unroll
             for (int k = 0; k < H2; k += 2) {
                 const uint4 gif = ld_shared_v4(gt_rd + (uint32_t)((k >> 1) * 256));               // i_k i_k+1 f_k f_k+1
@@ -553,10 +564,19 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             // (unit pair) x (two utterances) block, i.e. two 32-bit words: the validity protocol needs whole 32-bit words from one
             // thread (a word with one stale half must not pass the epoch check).  No shared-memory staging, no barrier.
             {
-                const uint32_t mine = wr_odd ? hp[1] : hp[0];
-                const uint32_t theirs = __shfl_xor_sync(0xffffffffu, wr_odd ? hp[0] : hp[1], 4);
-                const uint32_t ev = wr_odd ? theirs : mine, od = wr_odd ? mine : theirs;      // even unit / odd unit, same two utterances
-                const uint32_t w0 = __byte_perm(ev, od, 0x5410), w1 = __byte_perm(ev, od, 0x7632);
+                // HW = 2: w0 / w1 = the lane's first / second utterance.  HW = 1 (two utterances per lane, 16 warps): the even-unit lane
+                // stores the pair's word of the first utterance, the odd-unit lane that of the second.
+                uint32_t w0, w1 = 0u;
+                if constexpr (HW == 2) {
+                    const uint32_t mine = wr_odd ? hp[1] : hp[0];
+                    const uint32_t theirs = __shfl_xor_sync(0xffffffffu, wr_odd ? hp[0] : hp[1], 4);
+                    const uint32_t ev = wr_odd ? theirs : mine, od = wr_odd ? mine : theirs;      // even unit / odd unit, same two utterances
+                    w0 = __byte_perm(ev, od, 0x5410); w1 = __byte_perm(ev, od, 0x7632);
+                } else {
+                    const uint32_t theirs = __shfl_xor_sync(0xffffffffu, hp[0], 4);
+                    const uint32_t ev = wr_odd ? theirs : hp[0], od = wr_odd ? hp[0] : theirs;
+                    w0 = __byte_perm(ev, od, wr_odd ? 0x7632 : 0x5410);
+                }
                 if (t + 1 < a.T) {
                     uint32_t x0 = w0, x1 = w1;
                     if ((x0 | x1) & EPOCH_BITS) {      // non-finite h (never for finite inputs): +-1 in the exchange copy, see the header
@@ -570,10 +590,10 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     const uint32_t ptag = (((uint32_t)t >> 1) & 1u) * EPOCH_BITS;
                     char* yx = yx_wr + ((t & 1) ? slot_bytes : 0u);
                     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx), "r"(x0 | ptag) : "memory");
-                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx + PLANE_ELEMS * 2), "r"(x1 | ptag) : "memory");
+                    if constexpr (HW == 2) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(yx + PLANE_ELEMS * 2), "r"(x1 | ptag) : "memory");
                 }
                 if (y_ok0) *reinterpret_cast<uint32_t*>(y_wr) = w0;
-                if (y_ok1) *reinterpret_cast<uint32_t*>(y_wr + y_row_bytes) = w1;
+                if (HW == 2 && y_ok1) *reinterpret_cast<uint32_t*>(y_wr + y_row_bytes) = w1;
                 y_wr += y_step_bytes;
             }
             if (tg == 0) AVC_TRACE2(g, 4);
@@ -712,7 +732,7 @@ cudaError_t launch_ll_lstm(const LlLstmPlan* plan, cudaStream_t s, int* launches
         void* kargs[2] = {(void*)&plan->tmW, (void*)&args};
         // CTAs wait on one another's output: cooperative launch (guaranteed co-residency), with the checked non-cooperative
         // retry of launch_persistent() for profilers (AVC_LSTM_NOCOOP forces it)
-        e = launch_persistent(kernel_for(plan->nkb, plan->gx_f16, plan->nsub, tracing), plan->grids[i], dim3(threads(plan->nsub)), (size_t)plan->smem_bytes, 2,
+        e = launch_persistent(kernel_for(plan->nkb, plan->gx_f16, plan->nsub, tracing), plan->grids[i], dim3(threads(plan->nsub, plan->nkb)), (size_t)plan->smem_bytes, 2,
                               kargs, s, getenv("AVC_LSTM_NOCOOP") != nullptr);
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
