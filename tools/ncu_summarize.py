@@ -12,7 +12,9 @@ shutil.copy(os.path.join(go, "b_bf16.log"), os.path.join(out_dir, f"r2_bench_{ta
 keys = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__registers_per_thread', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
         'sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
         'sm__warps_active.avg.pct_of_peak_sustained_active', 'lts__t_sector_hit_rate.pct', 'lts__throughput.avg.pct_of_peak_sustained_elapsed',
-        'l1tex__m_xbar2l1tex_read_bytes.sum']
+        'l1tex__m_xbar2l1tex_read_bytes.sum', 'smsp__issue_active.avg.pct_of_peak_sustained_active', 'smsp__inst_issued.avg',
+        'smsp__average_warp_latency_per_inst_issued.ratio', 'l1tex__data_pipe_lsu_wavefronts_mem_shared_op_ld.sum',
+        'l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld.sum']
 out = [f"# ncu --set full summaries, round 2, capture {tag} (B200, config 2: B=256, T=128, bf16 mode)\n",
        f"Build: {desc}. Captured with `tools/gpu_ncu.sh`, summarised by `tools/ncu_summarize.py`. Per-launch values, cold cache,",
        "serialised - compare shares, not absolutes. Under ncu the cooperative cluster launch of the recurrence falls back to the checked",
