@@ -98,7 +98,8 @@ struct LlLstmArgs {
     int tiles, tile0;            // 32-utterance tiles in Yx, first tile of this launch
     long long y_sb, y_st;        // element strides of Y along utterance / frame
     long long gx_sb, gx_st;      // same for Gx rows (frame index t / gx_div)
-    uint32_t idesc;
+    uint32_t idesc;              // M = 256, N = 32
+    uint32_t idesc16;            // M = 256, N = 16: sub-tiles with at most 8 utterances (rows 0..7 of the leader CTA's operand tile)
     int approx;                  // 1 (default): gate activations with MUFU.TANH (tanh.approx.f32, abs err ~5e-4: below the bf16 rounding of h;
                                  // measured end-to-end error unchanged); AVC_LSTM_EXACT=1 selects ex2/rcp based sigmoid/tanh
     long long* trace;            // optional clock64 trace of CTA (0,0) (AVC_LSTM_TRACE=1), nullptr normally
@@ -286,6 +287,9 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     const uint32_t par = (uint32_t)(t - 1) & 1;
                     auto issue_sub = [&](auto G) {
                         constexpr int g = decltype(G)::value;
+                        // a sub-tile with <= 8 utterances: N = 16 MMAs (each CTA supplies rows 0..7 of its tile, the leader's are
+                        // utterances 0..7 = accumulator columns 0..7; the other columns belong to no utterance) - half the pipe time
+                        const uint32_t idesc = a.B - (bt * NSUB + g) * SUB_N <= 8 ? a.idesc16 : a.idesc;
                         constexpr uint32_t d_tmem = tmem_base + (uint32_t)((2 * g + ih) * SUB_N);
                         // Issue loop shape: ROLLED over the K chunks with running descriptor words.  ptxas then keeps the whole
                         // sequence on the uniform datapath (UIADD3 / UMOV between the UTCHMMAs); unrolled, it computes every
@@ -311,7 +315,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                                 for (int c = c0; c < ss_end; ++c) {
 #pragma unroll
                                     for (int k = 0; k < KBLK / 16; ++k) {
-                                        ptx::umma2_f16_warp(d_tmem, ((uint64_t)a_hi << 32) | a_lo, ((uint64_t)b_hi << 32) | b_lo, a.idesc,
+                                        ptx::umma2_f16_warp(d_tmem, ((uint64_t)a_hi << 32) | a_lo, ((uint64_t)b_hi << 32) | b_lo, idesc,
                                                             (c != ih * (NKB / 2) || k != 0) ? 1u : 0u);
                                         a_lo += 2; b_lo += 2;
                                     }
@@ -326,7 +330,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                                 for (int c = ss_end; c < c1; ++c) {
 #pragma unroll
                                     for (int k = 0; k < KBLK / 16; ++k) {
-                                        ptx::umma2_f16_ts_warp(d_tmem, a_t, ((uint64_t)b_hi << 32) | b_lo, a.idesc, (c != ih * (NKB / 2) || k != 0) ? 1u : 0u);
+                                        ptx::umma2_f16_ts_warp(d_tmem, a_t, ((uint64_t)b_hi << 32) | b_lo, idesc, (c != ih * (NKB / 2) || k != 0) ? 1u : 0u);
                                         a_t += 8; b_lo += 2;
                                     }
                                     b_lo += (uint32_t)(HBLK2 >> 4) - 2 * (KBLK / 16);
@@ -710,6 +714,7 @@ LlLstmPlan* ll_lstm_plan_create(const void* Whh_bf16, const void* Gx, int gx_typ
         a.tiles = ceil_div(B, tnp) * nsub; a.tile0 = bs / tnp * nsub;          // Yx is indexed in 32-row tiles
         a.approx = getenv("AVC_LSTM_EXACT") == nullptr;
         a.idesc = ptx::umma_idesc_f16(1, 2 * MROWS, SUB_N);          // the pair's MMA: M = 256 (128 gate rows per CTA), N = 32
+        a.idesc16 = getenv("AVC_LSTM_NO_N16") ? a.idesc : ptx::umma_idesc_f16(1, 2 * MROWS, 16);
         plan->args.push_back(a);
         plan->grids.push_back(dim3(G_n, ceil_div(Bc, tnp)));
     }
