@@ -23,11 +23,16 @@
 //       nothing else.  (With group barriers 15 % of all warp samples sat behind the group's slowest poller and 5 % in front of
 //       the stores; profiles/r2_ll_lstm_notes.md.)  Hence the Gx_t block is staged warp-privately, the 4x4 gate transpose goes
 //       through a per-warp shared-memory tile, and h_t leaves straight from registers.
+//   (3) The chain is serial code on warps that share a scheduler four or five ways: every instruction on a warp's path through a
+//       step costs ~9 cycles of the step (ncu source counters; profiles/r2_ll_lstm_notes.md).  Hence: nothing that does not
+//       depend on t is computed inside the time loop (ring / output / Gx source pointers, the remote barrier address and the
+//       accumulator address are built once and kept opaque to the compiler), Gx_t is fetched before the accumulator wait,
+//       the epilogue arithmetic is packed fp32x2, the transpose tile is bank-conflict free, and tracing has its own instantiation.
 //
 // Warp roles (NSUB x GW + 2 warps; GW = 8 group warps per sub-tile, 16 for the one sub-tile of an H = 1024 CTA - each warp then
 // owns half the chunks and half the columns):
 //   warps GW g..GW g + GW - 1   sub-tile g: loaders of its h_{t-1} rows (poll -> swizzled K-major operand tile -> fence.proxy.async ->
-//                    arrive on the mbarrier of its own K part in the leader CTA) AND its gate epilogue (tcgen05.ld of 16 columns per
+//                    arrive on the mbarrier of its own K part in the leader CTA) AND its gate epilogue (tcgen05.ld of 16 or 8 columns per
 //                    thread, + Gx_t, MUFU.TANH gates, cell update with c in registers, h_t stores)
 //   last two warps   MMA issuers (leader CTA), one K half each into its own accumulator, each strictly alternating
 //                    A(t), B(t), A(t+1), ... in program order.  That order (a) keeps the accumulation order independent of timing
