@@ -197,8 +197,13 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     uint64_t* acc_full = bars + 1;                             // [2] the MMAs (both K halves) of a sub-tile's step are complete
     uint64_t* gfull = bars + 4;                                // [2][PARTS] part p of sub-tile g's K chunks is in shared memory (both CTAs)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
-    uint64_t* wst_full = bars + 22;                            // [2] prologue: a 16 KiB chunk of W_hh has landed in staging buffer i
-    uint64_t* wst_empty = bars + 24;                           // [2] ... and has been moved on to tensor memory
+    uint64_t* wst_full = bars + 22;                            // [WST] prologue: a 16 KiB chunk of W_hh has landed in staging buffer i
+    uint64_t* wst_empty = bars + 26;                           // [WST] ... and has been moved on to tensor memory
+    // staging buffers of that prologue: as many 16 KiB chunks in flight as the not yet used operand / Gx / transpose areas hold, up
+    // to four (two in flight filled tensor memory at 12 B/clk: 7 of the launch's 19 fixed us)
+    constexpr int WST_ROOM = NSUB * (NKB * HBLK2 + 2 * gx2_bytes(GXH) + GT_BYTES) / W_BLK_BYTES;
+    constexpr int WST = WST_ROOM < 4 ? WST_ROOM : 4;
+    static_assert(WST >= 2, "the W_hh staging ring needs two buffers");
     // K is handed to the issuers in PARTS pieces.  One sub-tile: eight, each the chunks of two loader warps of either CTA - the
     // MMAs left to issue when the last piece of h_{t-1} lands are an eighth of the step's (same-box A/B: config 3 9.75 -> 9.57 ms,
     // B = 1 p50 1.18 -> 1.16 ms).  Two sub-tiles (and H = 256): quarters - there the issuers share their schedulers with the other
@@ -224,7 +229,7 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
             for (int i = 0; i < 2 * PARTS; ++i) ptx::mbar_init(&gfull[i], 2 * WPP);          // the part's loader warps of both CTAs
             ptx::mbar_init(&acc_full[0], 2);                                                 // one commit per issuing warp
             ptx::mbar_init(&acc_full[1], 2);
-            for (int i = 0; i < 2; ++i) { ptx::mbar_init(&wst_full[i], 1); ptx::mbar_init(&wst_empty[i], 4); }
+            for (int i = 0; i < WST; ++i) { ptx::mbar_init(&wst_full[i], 1); ptx::mbar_init(&wst_empty[i], 4); }
             ptx::fence_barrier_init();
         }
         __syncwarp();
@@ -244,13 +249,13 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
     // Gx area) -> registers (thread = gate row: eight conflict-free 16-byte reads) -> tcgen05.st.  One row per thread straight
     // from global memory (16 bytes per lane at a 2 KiB stride, a dependent round per chunk) took 7 of the launch's 19 fixed us.
     {
-        uint8_t* wstage = sH;                                  // 2 x 16 KiB; sH .. end of the Gx / transpose areas is >= 56 KiB in every instantiation
+        uint8_t* wstage = sH;                                  // WST x 16 KiB (sH .. end of the Gx / transpose areas)
         if (warp < 4) {
             const int R = warp * 32 + lane;
             const uint32_t wl = tmem_base + W_COL + ((uint32_t)(warp * 32) << 16);
             for (int sl = 0; sl < NKB_T; ++sl) {
-                const int st = sl & 1;
-                ptx::mbar_wait(&wst_full[st], (uint32_t)(sl >> 1) & 1);
+                const int st = sl % WST;
+                ptx::mbar_wait(&wst_full[st], (uint32_t)(sl / WST) & 1);
                 const uint32_t row = ptx::smem_u32(wstage) + (uint32_t)(st * W_BLK_BYTES + R * 128);
                 uint4 v[8];
 #pragma unroll
@@ -267,8 +272,8 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                     ptx::tma_load_2d(sW + j * W_BLK_BYTES, &tmW, wfull, ((j / (HS > 0 ? HS : 1)) * (NKB / 2) + j % (HS > 0 ? HS : 1)) * KBLK, ns * MROWS);
             }
             for (int sl = 0; sl < NKB_T; ++sl) {
-                const int st = sl & 1, kc = (sl / HT) * (NKB / 2) + HS + sl % HT;
-                if (sl >= 2) ptx::mbar_wait(&wst_empty[st], (uint32_t)((sl >> 1) - 1) & 1);
+                const int st = sl % WST, kc = (sl / HT) * (NKB / 2) + HS + sl % HT;
+                if (sl >= WST) ptx::mbar_wait(&wst_empty[st], (uint32_t)(sl / WST - 1) & 1);
                 ptx::mbar_expect_tx(&wst_full[st], (uint32_t)W_BLK_BYTES);
                 ptx::tma_load_2d(wstage + st * W_BLK_BYTES, &tmW, &wst_full[st], kc * KBLK, ns * MROWS);
             }
