@@ -483,7 +483,9 @@ ll_lstm_kernel(const __grid_constant__ CUtensorMap tmW, const LlLstmArgs a) {
                 }
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(gfull_remote) : "memory");   // both CTAs arrive
+                // both CTAs arrive on the leader's barrier.  Default semantics (release at CTA scope): a .release.cluster arrive compiles
+                // to MEMBAR.ALL.GPU - an L2 round trip per arrive - and the data it guards is shared memory behind fence.proxy.async
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(gfull_remote) : "memory");
                 if (tg == 0) AVC_TRACE2(g, 2);
                 if (lane == 0 && wg < 8) AVC_TRACE2(g, 16 + wg);
                 stage_gx(t + 1);

@@ -10,15 +10,6 @@ namespace ptx {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred = 0;
-    asm volatile(
-        "{\n\t.reg .pred P;\n\t"
-        "elect.sync _|P, 0xffffffff;\n\t"
-        "selp.u32 %0, 1, 0, P;\n\t}\n"
-        : "=r"(pred));
-    return pred != 0;
-}
 
 // ---- mbarrier -------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -56,7 +47,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 
 // ---- fences ---------------------------------------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -68,12 +58,6 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* m, uin
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
 
@@ -95,13 +79,6 @@ __device__ __forceinline__ void tma_load_3d_warp(void* dst, const CUtensorMap* m
         : "memory");
 }
 
-__device__ __forceinline__ void tma_load_3d_mc(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, uint16_t cta_mask) {
-    // multicast: the box lands at the same smem offset (and signals the mbarrier at the same offset) in every CTA of cta_mask
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], %6;"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(cta_mask)
-        : "memory");
-}
 
 // TMA store shared -> global (bulk async-group completion); out-of-range parts of the box are clipped
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* src, int c0, int c1, int c2) {
@@ -151,13 +128,6 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
     return r;
 }
-// arrive on the mbarrier at the same offset in CTA `rank` of the cluster.  Default semantics (release at CTA scope), as
-// CUTLASS's ClusterBarrier does: a .release.cluster arrive compiles to MEMBAR.ALL.GPU (a full L2 round trip per arrive)
-// and an .acquire.cluster wait adds CCTL.IVALL; the data these barriers guard is shared memory written behind
-// fence.proxy.async / tensor memory behind tcgen05 fences, not global memory.
-__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
-    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(mapa_u32(smem_u32(bar), rank)) : "memory");
-}
 template <uint32_t kCols>
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem) {  // one full warp (same warp id) in BOTH CTAs of the pair
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "n"(kCols) : "memory");
@@ -185,47 +155,6 @@ __device__ __forceinline__ void umma2_f16_ts_warp(uint32_t d_tmem, uint32_t a_tm
         "setp.ne.b32 p, %4, 0;\n\t"
         "@q tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n"
         ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// One 64-wide K chunk = four K=16 pair MMAs in one block: one election, TMEM addresses as immediates, the B descriptor
-// advanced inside (+2 per K step in the address field): fewer issue slots per MMA than four separate calls.
-template <uint32_t D_TMEM, uint32_t A_TMEM>
-__device__ __forceinline__ void umma2_f16_ts_chunk_warp(uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t accumulate_first) {
-    asm volatile(
-        "{\n\t.reg .pred p, q, one;\n\t.reg .b32 d, a0, a1, a2, a3, l1, l2, l3;\n\t.reg .b64 b0, b1, b2, b3;\n\t"
-        "elect.sync _|q, 0xffffffff;\n\t"
-        "setp.ne.b32 p, %3, 0;\n\t"
-        "setp.eq.b32 one, 0, 0;\n\t"
-        "mov.u32 d, %4;\n\t"
-        "mov.u32 a0, %5;\n\tadd.u32 a1, a0, 8;\n\tadd.u32 a2, a0, 16;\n\tadd.u32 a3, a0, 24;\n\t"
-        "add.u32 l1, %0, 2;\n\tadd.u32 l2, %0, 4;\n\tadd.u32 l3, %0, 6;\n\t"
-        "mov.b64 b0, {%0, %1};\n\tmov.b64 b1, {l1, %1};\n\tmov.b64 b2, {l2, %1};\n\tmov.b64 b3, {l3, %1};\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a0], b0, %2, p;\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a1], b1, %2, one;\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a2], b2, %2, one;\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], [a3], b3, %2, one;\n\t}\n"
-        ::"r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate_first), "n"(D_TMEM), "n"(A_TMEM)
-        : "memory");
-}
-// same with A from shared memory (descriptor advanced like B's)
-template <uint32_t D_TMEM>
-__device__ __forceinline__ void umma2_f16_ss_chunk_warp(uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
-                                                        uint32_t accumulate_first) {
-    asm volatile(
-        "{\n\t.reg .pred p, q, one;\n\t.reg .b32 d, l1, l2, l3, m1, m2, m3;\n\t.reg .b64 a0, a1, a2, a3, b0, b1, b2, b3;\n\t"
-        "elect.sync _|q, 0xffffffff;\n\t"
-        "setp.ne.b32 p, %5, 0;\n\t"
-        "setp.eq.b32 one, 0, 0;\n\t"
-        "mov.u32 d, %6;\n\t"
-        "add.u32 m1, %0, 2;\n\tadd.u32 m2, %0, 4;\n\tadd.u32 m3, %0, 6;\n\t"
-        "add.u32 l1, %2, 2;\n\tadd.u32 l2, %2, 4;\n\tadd.u32 l3, %2, 6;\n\t"
-        "mov.b64 a0, {%0, %1};\n\tmov.b64 a1, {m1, %1};\n\tmov.b64 a2, {m2, %1};\n\tmov.b64 a3, {m3, %1};\n\t"
-        "mov.b64 b0, {%2, %3};\n\tmov.b64 b1, {l1, %3};\n\tmov.b64 b2, {l2, %3};\n\tmov.b64 b3, {l3, %3};\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a0, b0, %4, p;\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a1, b1, %4, one;\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a2, b2, %4, one;\n\t"
-        "@q tcgen05.mma.cta_group::2.kind::f16 [d], a3, b3, %4, one;\n\t}\n"
-        ::"r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate_first), "n"(D_TMEM)
         : "memory");
 }
 // arrives on the mbarrier at this offset in BOTH CTAs of the pair when the issuing thread's MMAs have completed
@@ -276,15 +205,6 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint6
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-// D[tmem] (+)= A[tmem] * B[smem]^T: A is M lanes x K elements packed two 16-bit values per 32-bit column (K = 16 -> 8 columns)
-__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
 // Whole-warp variants: every lane executes the call with warp-uniform operands and ONE elected lane issues.  With the
 // operands provably uniform the compiler keeps them in uniform registers; an `if (lane == 0)` around umma_f16 instead
 // makes it wrap every UTCHMMA in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~100 cycles of issue per MMA).
@@ -295,15 +215,6 @@ __device__ __forceinline__ void umma_f16_warp(uint32_t d_tmem, uint64_t a_desc, 
         "setp.ne.b32 p, %4, 0;\n\t"
         "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void umma_f16_ts_warp(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .pred q;\n\t"
-        "elect.sync _|q, 0xffffffff;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 __device__ __forceinline__ void umma_commit_warp(uint64_t* bar) {
